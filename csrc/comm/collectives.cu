@@ -1,0 +1,475 @@
+// Peer-memory collectives over NVLink 5 / NVSwitch, with the optimizer fused in.
+//
+// Every rank owns "symmetric" buffers (same size on every rank) and holds a
+// table of pointers to each peer's copy (CUDA IPC across processes, plain peer
+// access inside one process).  Kernels read and write peer memory directly
+// with ordinary ld/st; ordering between ranks uses system-scope release /
+// acquire on per-rank flag words with a monotonically increasing epoch that
+// lives in device memory, so the same launch can be replayed from a CUDA graph.
+//
+//   one-shot : every rank reads all W copies of the whole bucket and reduces
+//              locally (latency optimal, W x read traffic; small buckets)
+//   two-shot : rank r reduces slice r from all W copies, then stores the
+//              result into all W destinations (bandwidth optimal on NVSwitch)
+//
+// The fused variants apply cast + 1/W + weight decay + SGD-momentum or Adam to
+// the reduced gradient and (two-shot) scatter the *updated parameters* instead
+// of gradients, so gradient all-reduce, averaging and optimizer.step() are one
+// kernel and one pass over memory.
+//
+// Reductions always sum ranks in rank order 0..W-1, so every rank computes
+// bit-identical results and runs are reproducible.
+//
+// Capability covered: K-C1, K-C2, K-C3, K-C5, K-C7, K-C8, K-C10, K-C11, K-O14,
+// K-O15 of SURVEY.md section 2.5 (the reference reaches NCCL through
+// DistributedDataParallel / DataParallel and torch.optim.SGD:
+// pytorch/distributed_data_parallel.py:74,94-95,132-133; pytorch/data_parallel.py:71,108-109).
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+#include "../../include/dtdl_b200.h"
+
+#include <string.h>
+
+namespace dtdl {
+
+static constexpr int kMaxWorld = 16;
+
+struct CommDev {
+  int rank, world;
+  uint32_t* flags_local;           // [2][kMaxWorld]: START row, DONE row
+  uint32_t* flags_peer[kMaxWorld]; // peers' flags_local
+  uint32_t* epoch;                 // device word, last completed epoch
+  uint32_t* counter;               // device word, finished-block ticket
+};
+
+struct CommHost {
+  CommDev d;
+  int device;
+};
+
+struct PeerPtrs {
+  void* p[kMaxWorld];
+};
+
+// hyper-parameter block in device memory (written by the host before a step)
+//  [0] lr  [1] momentum  [2] weight_decay  [3] inv_world  [4] beta1  [5] beta2
+//  [6] eps [7] bias_correction1  [8] bias_correction2_sqrt  [9] dampening
+enum { H_LR = 0, H_MOM, H_WD, H_INVW, H_B1, H_B2, H_EPS, H_BC1, H_BC2S, H_DAMP };
+
+enum { OPT_NONE = 0, OPT_SGD = 1, OPT_ADAM = 2, OPT_ADAM_KERAS = 3 };
+
+__device__ __forceinline__ void spin_until_ge(const uint32_t* p, uint32_t want, int tag) {
+  long long t0 = clock64();
+  while ((int32_t)(ld_acquire_sys(p) - want) < 0) {
+    if (clock64() - t0 > DTDL_SPIN_TIMEOUT_CYCLES) {
+      printf("[dtdl] peer flag wait timed out (tag %d): block %d thread %d want %u have %u\n", tag,
+             blockIdx.x, threadIdx.x, want, ld_relaxed_sys(p));
+      __trap();
+    }
+  }
+}
+
+// All blocks: wait until every rank has announced epoch e on the START row.
+__device__ __forceinline__ void comm_start(const CommDev& c, uint32_t e) {
+  if (c.world == 1) return;
+  if (blockIdx.x == 0 && threadIdx.x < c.world) {
+    __threadfence_system();
+    st_release_sys(c.flags_peer[threadIdx.x] + c.rank, e);
+  }
+  if (threadIdx.x < c.world) spin_until_ge(c.flags_local + threadIdx.x, e, 1);
+  __syncthreads();
+}
+
+// All blocks: the last block to arrive announces DONE to every rank, waits for
+// every rank's DONE (so nobody still reads or writes our buffers when the
+// kernel exits) and publishes the epoch.
+__device__ __forceinline__ void comm_finish(const CommDev& c, uint32_t e) {
+  __threadfence_system();
+  __syncthreads();
+  __shared__ int is_last;
+  if (threadIdx.x == 0) {
+    const unsigned ticket = atomicAdd(c.counter, 1u);
+    is_last = (ticket == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!is_last) return;
+  if (c.world > 1) {
+    if (threadIdx.x < c.world) {
+      __threadfence_system();
+      st_release_sys(c.flags_peer[threadIdx.x] + kMaxWorld + c.rank, e);
+      spin_until_ge(c.flags_local + kMaxWorld + threadIdx.x, e, 2);
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    *c.counter = 0;
+    *c.epoch = e;
+    __threadfence();
+  }
+}
+
+__device__ __forceinline__ float4 f4_add(float4 a, float4 b) {
+  return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* base, long long i4) {
+  // peer reads bypass the local L2; keep them out of L1 too (data is read once)
+  return ld_nc_f4(reinterpret_cast<const float4*>(base) + i4);
+}
+
+__device__ __forceinline__ float sgd_one(float g, float& p, float& m, const float* h) {
+  g = g * h[H_INVW] + h[H_WD] * p;
+  m = h[H_MOM] * m + (1.f - h[H_DAMP]) * g;
+  p -= h[H_LR] * m;
+  return p;
+}
+__device__ __forceinline__ float adam_one(float g, float& p, float& m, float& v, const float* h,
+                                          int keras) {
+  g = g * h[H_INVW] + h[H_WD] * p;
+  m = h[H_B1] * m + (1.f - h[H_B1]) * g;
+  v = h[H_B2] * v + (1.f - h[H_B2]) * g * g;
+  if (keras) {
+    // lr_t = lr * sqrt(1-b2^t)/(1-b1^t);  p -= lr_t * m / (sqrt(v) + eps)
+    p -= h[H_LR] * h[H_BC2S] / h[H_BC1] * m / (sqrtf(v) + h[H_EPS]);
+  } else {
+    p -= (h[H_LR] / h[H_BC1]) * m / (sqrtf(v) / h[H_BC2S] + h[H_EPS]);
+  }
+  return p;
+}
+
+struct ReduceArgs {
+  PeerPtrs grads;    // fp32 gradient bucket on every rank (same offset everywhere)
+  PeerPtrs dst;      // two-shot plain: reduced output on every rank; fused: params on every rank
+  float* param;      // local params   (fused)
+  float* mom;        // local momentum / Adam m (fused)
+  float* var;        // local Adam v
+  const float* hyper;
+  long long n;       // elements, multiple of 4
+  int opt;           // OPT_*
+  int two_shot;
+  float scale;       // plain all-reduce: multiply the sum by this (1 or 1/W)
+};
+
+// One kernel for every (variant, optimizer) pair; branches are grid-uniform.
+__global__ void __launch_bounds__(512)
+reduce_kernel(const CommDev c, const ReduceArgs a) {
+  const uint32_t e = *c.epoch + 1;
+  comm_start(c, e);
+
+  const int W = c.world;
+  long long begin4 = 0, end4 = a.n / 4;
+  if (a.two_shot && W > 1) {
+    const long long per = (end4 + W - 1) / W;
+    begin4 = per * c.rank;
+    end4 = begin4 + per < end4 ? begin4 + per : end4;
+    if (begin4 > end4) begin4 = end4;
+  }
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = begin4 + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < end4;
+       i += stride) {
+    float4 s = ld_peer_f4(reinterpret_cast<const float*>(a.grads.p[0]), i);
+    for (int r = 1; r < W; ++r) s = f4_add(s, ld_peer_f4(reinterpret_cast<const float*>(a.grads.p[r]), i));
+    float4 out;
+    if (a.opt == OPT_NONE) {
+      out = make_float4(s.x * a.scale, s.y * a.scale, s.z * a.scale, s.w * a.scale);
+    } else {
+      float4 p = reinterpret_cast<float4*>(a.param)[i];
+      float4 m = reinterpret_cast<float4*>(a.mom)[i];
+      if (a.opt == OPT_SGD) {
+        sgd_one(s.x, p.x, m.x, a.hyper);
+        sgd_one(s.y, p.y, m.y, a.hyper);
+        sgd_one(s.z, p.z, m.z, a.hyper);
+        sgd_one(s.w, p.w, m.w, a.hyper);
+      } else {
+        float4 v = reinterpret_cast<float4*>(a.var)[i];
+        const int keras = a.opt == OPT_ADAM_KERAS;
+        adam_one(s.x, p.x, m.x, v.x, a.hyper, keras);
+        adam_one(s.y, p.y, m.y, v.y, a.hyper, keras);
+        adam_one(s.z, p.z, m.z, v.z, a.hyper, keras);
+        adam_one(s.w, p.w, m.w, v.w, a.hyper, keras);
+        reinterpret_cast<float4*>(a.var)[i] = v;
+      }
+      reinterpret_cast<float4*>(a.mom)[i] = m;
+      out = p;
+    }
+    if (a.two_shot && W > 1) {
+      for (int r = 0; r < W; ++r) reinterpret_cast<float4*>(a.dst.p[r])[i] = out;
+    } else {
+      reinterpret_cast<float4*>(a.dst.p[c.rank])[i] = out;
+    }
+  }
+  comm_finish(c, e);
+}
+
+// Every non-root rank pulls `n16` 16-byte words from the root's copy.
+__global__ void __launch_bounds__(512)
+broadcast_kernel(const CommDev c, const PeerPtrs buf, long long n16, int root) {
+  const uint32_t e = *c.epoch + 1;
+  comm_start(c, e);
+  if (c.rank != root) {
+    const uint4* src = reinterpret_cast<const uint4*>(buf.p[root]);
+    uint4* dst = reinterpret_cast<uint4*>(buf.p[c.rank]);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += stride)
+      dst[i] = src[i];
+  }
+  comm_finish(c, e);
+}
+
+// all-gather: rank r pushes its slice of `buf` into every peer's copy.
+__global__ void __launch_bounds__(512)
+allgather_kernel(const CommDev c, const PeerPtrs buf, long long n16) {
+  const uint32_t e = *c.epoch + 1;
+  comm_start(c, e);
+  const int W = c.world;
+  const long long per = (n16 + W - 1) / W;
+  const long long b = per * c.rank;
+  const long long en = b + per < n16 ? b + per : n16;
+  const uint4* src = reinterpret_cast<const uint4*>(buf.p[c.rank]);
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = b + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < en; i += stride) {
+    const uint4 v = src[i];
+    for (int r = 0; r < W; ++r)
+      if (r != c.rank) reinterpret_cast<uint4*>(buf.p[r])[i] = v;
+  }
+  comm_finish(c, e);
+}
+
+__global__ void barrier_kernel(const CommDev c) {
+  const uint32_t e = *c.epoch + 1;
+  comm_start(c, e);
+  comm_finish(c, e);
+}
+
+// Single-rank optimizer step on a flat fp32 arena (W = 1, no flags touched).
+__global__ void __launch_bounds__(512)
+local_update_kernel(float* __restrict__ param, const float* __restrict__ grad,
+                    float* __restrict__ mom, float* __restrict__ var,
+                    const float* __restrict__ hyper, long long n4, int opt) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const float4 g = reinterpret_cast<const float4*>(grad)[i];
+    float4 p = reinterpret_cast<float4*>(param)[i];
+    float4 m = reinterpret_cast<float4*>(mom)[i];
+    if (opt == OPT_SGD) {
+      sgd_one(g.x, p.x, m.x, hyper);
+      sgd_one(g.y, p.y, m.y, hyper);
+      sgd_one(g.z, p.z, m.z, hyper);
+      sgd_one(g.w, p.w, m.w, hyper);
+    } else {
+      float4 v = reinterpret_cast<float4*>(var)[i];
+      const int keras = opt == OPT_ADAM_KERAS;
+      adam_one(g.x, p.x, m.x, v.x, hyper, keras);
+      adam_one(g.y, p.y, m.y, v.y, hyper, keras);
+      adam_one(g.z, p.z, m.z, v.z, hyper, keras);
+      adam_one(g.w, p.w, m.w, v.w, hyper, keras);
+      reinterpret_cast<float4*>(var)[i] = v;
+    }
+    reinterpret_cast<float4*>(mom)[i] = m;
+    reinterpret_cast<float4*>(param)[i] = p;
+  }
+}
+
+static int comm_grid(long long n4, int world, int two_shot, int max_blocks) {
+  long long per_rank = (two_shot && world > 1) ? (n4 + world - 1) / world : n4;
+  long long g = (per_rank + 512 * 4 - 1) / (512 * 4);
+  if (g > max_blocks) g = max_blocks;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+}  // namespace dtdl
+
+using namespace dtdl;
+#define STREAM(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" int dtdl_comm_create(int rank, int world, void** handle, void** flags_ptr) {
+  DTDL_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, "bad rank/world");
+  CommHost* h = new CommHost();
+  memset(h, 0, sizeof(*h));
+  h->d.rank = rank;
+  h->d.world = world;
+  DTDL_CHECK_CUDA(cudaGetDevice(&h->device));
+  uint32_t* mem = nullptr;
+  // flags + epoch + counter in one allocation: [2*kMaxWorld flags][epoch][counter]
+  DTDL_CHECK_CUDA(cudaMalloc(&mem, (2 * kMaxWorld + 2) * sizeof(uint32_t)));
+  DTDL_CHECK_CUDA(cudaMemset(mem, 0, (2 * kMaxWorld + 2) * sizeof(uint32_t)));
+  h->d.flags_local = mem;
+  h->d.epoch = mem + 2 * kMaxWorld;
+  h->d.counter = mem + 2 * kMaxWorld + 1;
+  h->d.flags_peer[rank] = mem;
+  *handle = h;
+  *flags_ptr = mem;
+  return 0;
+}
+
+extern "C" int dtdl_comm_set_peer_flags(void* handle, int peer, void* flags_ptr) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  DTDL_REQUIRE(peer >= 0 && peer < h->d.world, "bad peer");
+  h->d.flags_peer[peer] = reinterpret_cast<uint32_t*>(flags_ptr);
+  return 0;
+}
+
+extern "C" int dtdl_comm_destroy(void* handle) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  if (h) {
+    cudaFree(h->d.flags_local);
+    delete h;
+  }
+  return 0;
+}
+
+extern "C" int dtdl_symm_alloc(long long bytes, void** ptr) {
+  DTDL_REQUIRE(bytes > 0, "bad size");
+  const long long padded = (bytes + 255) / 256 * 256;
+  DTDL_CHECK_CUDA(cudaMalloc(ptr, (size_t)padded));
+  DTDL_CHECK_CUDA(cudaMemset(*ptr, 0, (size_t)padded));
+  return 0;
+}
+extern "C" int dtdl_symm_free(void* ptr) {
+  DTDL_CHECK_CUDA(cudaFree(ptr));
+  return 0;
+}
+extern "C" int dtdl_ipc_get_handle(void* ptr, void* out64) {
+  cudaIpcMemHandle_t h;
+  DTDL_CHECK_CUDA(cudaIpcGetMemHandle(&h, ptr));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is expected to be 64 bytes");
+  memcpy(out64, &h, 64);
+  return 0;
+}
+extern "C" int dtdl_ipc_open_handle(const void* in64, void** ptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, in64, 64);
+  DTDL_CHECK_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+extern "C" int dtdl_ipc_close_handle(void* ptr) {
+  DTDL_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}
+extern "C" int dtdl_enable_peer_access(int dev, int peer) {
+  int can = 0;
+  DTDL_CHECK_CUDA(cudaDeviceCanAccessPeer(&can, dev, peer));
+  DTDL_REQUIRE(can, "devices cannot access each other's memory");
+  int cur = 0;
+  DTDL_CHECK_CUDA(cudaGetDevice(&cur));
+  DTDL_CHECK_CUDA(cudaSetDevice(dev));
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) {
+    cudaGetLastError();
+    e = cudaSuccess;
+  }
+  cudaSetDevice(cur);
+  DTDL_CHECK_CUDA(e);
+  return 0;
+}
+
+static int fill_peers(PeerPtrs* pp, void* const* ptrs, int world, long long offset_bytes) {
+  memset(pp, 0, sizeof(*pp));
+  for (int r = 0; r < world; ++r) {
+    if (ptrs[r] == nullptr) return 1;
+    pp->p[r] = reinterpret_cast<char*>(ptrs[r]) + offset_bytes;
+  }
+  return 0;
+}
+
+extern "C" int dtdl_comm_barrier(void* handle, void* stream) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  barrier_kernel<<<1, 32, 0, STREAM(stream)>>>(h->d);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Plain all-reduce (sum * scale) of n fp32 elements at byte offset `offset` of
+// the symmetric buffer whose per-rank base pointers are grads[0..W).  The
+// result lands in dst[rank] (one-shot) or in every dst[r] (two-shot).
+extern "C" int dtdl_comm_allreduce(void* handle, void* const* grads, void* const* dst,
+                                   long long offset_bytes, long long n, float scale, int two_shot,
+                                   int max_blocks, void* stream) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  DTDL_REQUIRE(n % 4 == 0 && offset_bytes % 16 == 0, "buckets must be 16-byte granular");
+  ReduceArgs a;
+  memset(&a, 0, sizeof(a));
+  DTDL_REQUIRE(!fill_peers(&a.grads, grads, h->d.world, offset_bytes), "missing peer pointer");
+  DTDL_REQUIRE(!fill_peers(&a.dst, dst, h->d.world, offset_bytes), "missing peer pointer");
+  a.n = n;
+  a.opt = OPT_NONE;
+  a.two_shot = two_shot;
+  a.scale = scale;
+  const int grid = comm_grid(n / 4, h->d.world, two_shot, max_blocks > 0 ? max_blocks : 64);
+  reduce_kernel<<<grid, 512, 0, STREAM(stream)>>>(h->d, a);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Fused gradient all-reduce + 1/W + weight decay + SGD-momentum / Adam update.
+// params[r] are the per-rank base pointers of the symmetric parameter arena,
+// mom / var the local optimizer-state arenas, all addressed at `offset_bytes`.
+extern "C" int dtdl_comm_reduce_update(void* handle, void* const* grads, void* const* params,
+                                       float* mom, float* var, const float* hyper,
+                                       long long offset_bytes, long long n, int opt, int two_shot,
+                                       int max_blocks, void* stream) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  DTDL_REQUIRE(n % 4 == 0 && offset_bytes % 16 == 0, "buckets must be 16-byte granular");
+  DTDL_REQUIRE(opt == OPT_SGD || opt == OPT_ADAM || opt == OPT_ADAM_KERAS, "unknown optimizer");
+  ReduceArgs a;
+  memset(&a, 0, sizeof(a));
+  DTDL_REQUIRE(!fill_peers(&a.grads, grads, h->d.world, offset_bytes), "missing peer pointer");
+  DTDL_REQUIRE(!fill_peers(&a.dst, params, h->d.world, offset_bytes), "missing peer pointer");
+  a.param = reinterpret_cast<float*>(a.dst.p[h->d.rank]);
+  a.mom = reinterpret_cast<float*>(reinterpret_cast<char*>(mom) + offset_bytes);
+  a.var = var ? reinterpret_cast<float*>(reinterpret_cast<char*>(var) + offset_bytes) : nullptr;
+  DTDL_REQUIRE(opt == OPT_SGD || a.var != nullptr, "Adam needs the second-moment arena");
+  a.hyper = hyper;
+  a.n = n;
+  a.opt = opt;
+  a.two_shot = two_shot;
+  a.scale = 1.f;
+  const int grid = comm_grid(n / 4, h->d.world, two_shot, max_blocks > 0 ? max_blocks : 64);
+  reduce_kernel<<<grid, 512, 0, STREAM(stream)>>>(h->d, a);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_comm_broadcast(void* handle, void* const* bufs, long long offset_bytes,
+                                   long long bytes, int root, int max_blocks, void* stream) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  DTDL_REQUIRE(bytes % 16 == 0 && offset_bytes % 16 == 0, "buffers must be 16-byte granular");
+  PeerPtrs pp;
+  DTDL_REQUIRE(!fill_peers(&pp, bufs, h->d.world, offset_bytes), "missing peer pointer");
+  const long long n16 = bytes / 16;
+  long long g = (n16 + 2047) / 2048;
+  const int cap = max_blocks > 0 ? max_blocks : 64;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  broadcast_kernel<<<(int)g, 512, 0, STREAM(stream)>>>(h->d, pp, n16, root);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_comm_allgather(void* handle, void* const* bufs, long long offset_bytes,
+                                   long long bytes, int max_blocks, void* stream) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  DTDL_REQUIRE(bytes % 16 == 0 && offset_bytes % 16 == 0, "buffers must be 16-byte granular");
+  PeerPtrs pp;
+  DTDL_REQUIRE(!fill_peers(&pp, bufs, h->d.world, offset_bytes), "missing peer pointer");
+  const long long n16 = bytes / 16;
+  long long g = (n16 / h->d.world + 2047) / 2048;
+  const int cap = max_blocks > 0 ? max_blocks : 64;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  allgather_kernel<<<(int)g, 512, 0, STREAM(stream)>>>(h->d, pp, n16);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_local_update(float* param, const float* grad, float* mom, float* var,
+                                 const float* hyper, long long n, int opt, void* stream) {
+  DTDL_REQUIRE(n % 4 == 0, "arena must be a multiple of 4 elements");
+  DTDL_REQUIRE(opt == OPT_SGD || var != nullptr, "Adam needs the second-moment arena");
+  long long g = (n / 4 + 2047) / 2048;
+  if (g > 148 * 4) g = 148 * 4;
+  if (g < 1) g = 1;
+  local_update_kernel<<<(int)g, 512, 0, STREAM(stream)>>>(param, grad, mom, var, hyper, n / 4, opt);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,299 @@
+// Implicit-GEMM convolution / linear forward (and data-gradient) for sm_100a.
+//
+//   y[n,ho,wo,co] = sum_{r,s,ci} x[n, ho+r-pad_h, wo+s-pad_w, ci] * w[co, (r,s), ci]   (stride 1)
+//
+// GEMM view: M = output pixels (128 per CTA), N = output channels, K = taps x
+// input channels.  Nothing is im2col'ed: for each filter tap the A operand is
+// the *same* NHWC activation tensor loaded by a 4-D tiled TMA box shifted by
+// (s-pad_w, r-pad_h); out-of-image elements (the zero padding) and the channel
+// tail come back as zeros from the TMA unit.  B is the packed bf16 weight
+// matrix [Cout_p16][taps*Cin_p] (K-major).  Both land in shared memory in the
+// 128-byte-swizzled K-major layout tcgen05.mma consumes directly; the fp32
+// accumulator lives in TMEM and is drained by four epilogue warps.
+//
+// Roles (256 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected
+// lane), warp 2 = TMEM allocator, warps 4-7 = epilogue (TMEM -> regs -> global,
+// with optional bias / ReLU and bf16 or fp32 output).
+//
+// The data-gradient of a stride-1 convolution is the same kernel run on dy
+// with the tap-flipped, channel-transposed weight pack (see pack.cu); a Linear
+// layer is the 1x1 case with H = W = 1.
+//
+// Capability covered: K-O1/K-O3/K-O12/K-O20/K-O21 of SURVEY.md section 2.5 (the
+// reference reaches cuDNN/cuBLAS through nn.Conv2d / nn.Linear:
+// pytorch/model.py:28-32,62-63,77).
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+#include "../../include/dtdl_b200.h"
+
+namespace dtdl {
+
+struct ConvGemmArgs {
+  int taps, KW, pad_h, pad_w;
+  int chunks;       // ceil(Cin_p / 64): 64-channel K blocks per tap
+  int last_slices;  // UMMA_K(=16) slices that carry data in the last chunk
+  int Cin_p;        // K extent per tap inside the weight pack
+  int BW, BH, BNi, rows;
+  int tiles_w, tiles_h, tiles_n;
+  int Ho, Wo, N;
+  int Cout_p;  // channels per output pixel row
+  int n_tile;  // N per CTA, multiple of 16, <= 256
+  int tmem_cols;
+  int stages;
+  int b_stage_bytes;
+  int flags;  // 1 = ReLU, 2 = fp32 output
+  void* y;
+  const float* bias;
+};
+
+static constexpr int kAStage = 128 * 128;  // 128 pixel rows x 64 bf16
+
+__global__ void __launch_bounds__(256, 1)
+conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 const ConvGemmArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + a.stages * kAStage;
+  uint64_t* full = reinterpret_cast<uint64_t*>(sB + a.stages * a.b_stage_bytes);
+  uint64_t* empty = full + a.stages;
+  uint64_t* tmem_full = empty + a.stages;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  // tile coordinates
+  int mt = blockIdx.x;
+  const int tw_i = mt % a.tiles_w;
+  mt /= a.tiles_w;
+  const int th_i = mt % a.tiles_h;
+  const int tn_i = mt / a.tiles_h;
+  const int w0 = tw_i * a.BW, h0 = th_i * a.BH, n0 = tn_i * a.BNi;
+  const int nt = blockIdx.y;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < a.stages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_ptr, (uint32_t)a.tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  const int n_kblocks = a.taps * a.chunks;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      const uint32_t tx = (uint32_t)(a.rows * 128 + a.n_tile * 128);
+      int stage = 0, phase = 0;
+      for (int t = 0; t < a.taps; ++t) {
+        const int r = t / a.KW, s = t % a.KW;
+        for (int c = 0; c < a.chunks; ++c) {
+          mbar_wait(&empty[stage], phase ^ 1, 1);
+          mbar_arrive_expect_tx(&full[stage], tx);
+          tma_load_4d(sA + stage * kAStage, &tmA, &full[stage], c * 64, w0 + s - a.pad_w,
+                      h0 + r - a.pad_h, n0);
+          tma_load_2d(sB + stage * a.b_stage_bytes, &tmB, &full[stage], t * a.Cin_p + c * 64,
+                      nt * a.n_tile);
+          if (++stage == a.stages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      const uint32_t idesc = umma_idesc_bf16(128, a.n_tile, 0, 0);
+      const uint32_t sA_addr = smem_u32(sA), sB_addr = smem_u32(sB);
+      int stage = 0, phase = 0;
+      for (int kb = 0; kb < n_kblocks; ++kb) {
+        const int c = kb % a.chunks;
+        mbar_wait(&full[stage], phase, 2);
+        tc_fence_after();
+        const int nsl = (c == a.chunks - 1) ? a.last_slices : 4;
+        for (int k = 0; k < nsl; ++k) {
+          const uint64_t ad = umma_smem_desc(sA_addr + stage * kAStage + k * 32, 16, 1024);
+          const uint64_t bd = umma_smem_desc(sB_addr + stage * a.b_stage_bytes + k * 32, 16, 1024);
+          umma_bf16(tmem_base, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(&empty[stage]);
+        if (++stage == a.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit(tmem_full);
+    }
+  } else if (warp >= 4) {
+    const int q = warp - 4;
+    const int row = q * 32 + lane;
+    const int wi = row % a.BW;
+    const int hi = (row / a.BW) % a.BH;
+    const int ni = row / (a.BW * a.BH);
+    const int wo = w0 + wi, ho = h0 + hi, n = n0 + ni;
+    const bool valid = row < a.rows && wo < a.Wo && ho < a.Ho && n < a.N;
+    const size_t pix = ((size_t)n * a.Ho + ho) * a.Wo + wo;
+    const bool relu = a.flags & 1;
+    const bool f32 = a.flags & 2;
+
+    mbar_wait(tmem_full, 0, 3);
+    tc_fence_after();
+    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+    for (int j = 0; j < a.n_tile / 16; ++j) {
+      uint32_t v[16];
+      tmem_ld16(lane_base + j * 16, v);
+      tmem_ld_wait();
+      const int col0 = nt * a.n_tile + j * 16;
+      if (!valid) continue;
+      float f[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        f[i] = __uint_as_float(v[i]);
+        if (a.bias != nullptr && col0 + i < a.Cout_p) f[i] += a.bias[col0 + i];
+        if (relu) f[i] = fmaxf(f[i], 0.f);
+      }
+      if (f32) {
+        float* out = reinterpret_cast<float*>(a.y) + pix * a.Cout_p + col0;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          if (col0 + i < a.Cout_p) out[i] = f[i];
+      } else {
+        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(a.y) + pix * a.Cout_p + col0;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          if (col0 + h * 8 < a.Cout_p) {
+            uint4 pk;
+            __nv_bfloat162 p0 = __floats2bfloat162_rn(f[h * 8 + 0], f[h * 8 + 1]);
+            __nv_bfloat162 p1 = __floats2bfloat162_rn(f[h * 8 + 2], f[h * 8 + 3]);
+            __nv_bfloat162 p2 = __floats2bfloat162_rn(f[h * 8 + 4], f[h * 8 + 5]);
+            __nv_bfloat162 p3 = __floats2bfloat162_rn(f[h * 8 + 6], f[h * 8 + 7]);
+            pk.x = *reinterpret_cast<uint32_t*>(&p0);
+            pk.y = *reinterpret_cast<uint32_t*>(&p1);
+            pk.z = *reinterpret_cast<uint32_t*>(&p2);
+            pk.w = *reinterpret_cast<uint32_t*>(&p3);
+            *reinterpret_cast<uint4*>(out + h * 8) = pk;
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, (uint32_t)a.tmem_cols);
+}
+
+// Pixel tile (BW x BH x BNi <= 128 rows) shared by fprop and wgrad so both see
+// the same decomposition of the output image.
+void choose_pixel_tile(int N, int Ho, int Wo, int* BW, int* BH, int* BNi) {
+  int bw = Wo < 128 ? Wo : 128;
+  int bh = 128 / bw;
+  if (bh > Ho) bh = Ho;
+  if (bh < 1) bh = 1;
+  int bn = 1;
+  if (bh == Ho && bw == Wo) {
+    bn = 128 / (bw * bh);
+    if (bn > N) bn = N;
+    if (bn < 1) bn = 1;
+  }
+  *BW = bw;
+  *BH = bh;
+  *BNi = bn;
+}
+
+}  // namespace dtdl
+
+using namespace dtdl;
+
+extern "C" int dtdl_conv_fprop(const void* x, const void* wpack, void* y, const float* bias, int N,
+                               int H, int W, int Cin_p, int Ho, int Wo, int Cout_p, int KH, int KW,
+                               int pad_h, int pad_w, int flags, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  DTDL_REQUIRE(Cin_p % 8 == 0 && Cout_p % 8 == 0, "channel counts must be padded to 8");
+  DTDL_REQUIRE(Ho == H + 2 * pad_h - KH + 1 && Wo == W + 2 * pad_w - KW + 1,
+               "output size does not match a stride-1 convolution");
+  ConvGemmArgs a;
+  a.taps = KH * KW;
+  a.KW = KW;
+  a.pad_h = pad_h;
+  a.pad_w = pad_w;
+  a.chunks = (Cin_p + 63) / 64;
+  a.last_slices = (Cin_p - 64 * (a.chunks - 1) + 15) / 16;
+  a.Cin_p = Cin_p;
+  choose_pixel_tile(N, Ho, Wo, &a.BW, &a.BH, &a.BNi);
+  a.rows = a.BW * a.BH * a.BNi;
+  a.tiles_w = (Wo + a.BW - 1) / a.BW;
+  a.tiles_h = (Ho + a.BH - 1) / a.BH;
+  a.tiles_n = (N + a.BNi - 1) / a.BNi;
+  a.Ho = Ho;
+  a.Wo = Wo;
+  a.N = N;
+  a.Cout_p = Cout_p;
+  const int Np16 = (Cout_p + 15) / 16 * 16;
+  const int m_tiles = a.tiles_w * a.tiles_h * a.tiles_n;
+  int n_tile;
+  if (Np16 <= 256) {
+    int split = 1;
+    while (split < 4 && m_tiles * split < 120 && Np16 / (split + 1) >= 32) ++split;
+    n_tile = ((Np16 + split - 1) / split + 15) / 16 * 16;
+  } else {
+    n_tile = (m_tiles * ((Np16 + 255) / 256) >= 148) ? 256 : 128;
+  }
+  a.n_tile = n_tile;
+  const int n_tiles = (Np16 + n_tile - 1) / n_tile;
+  a.tmem_cols = n_tile <= 32 ? 32 : n_tile <= 64 ? 64 : n_tile <= 128 ? 128 : 256;
+  a.b_stage_bytes = (n_tile * 128 + 1023) / 1024 * 1024;
+  const int stage_bytes = kAStage + a.b_stage_bytes;
+  int stages = (200 * 1024) / stage_bytes;
+  if (stages > 8) stages = 8;
+  const int n_kblocks = a.taps * a.chunks;
+  if (stages > n_kblocks) stages = n_kblocks < 2 ? 2 : n_kblocks;
+  a.stages = stages;
+  a.flags = flags;
+  a.y = y;
+  a.bias = bias;
+
+  CUtensorMap tmA, tmB;
+  {
+    uint64_t dims[4] = {(uint64_t)Cin_p, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    uint64_t str[3] = {(uint64_t)Cin_p * 2, (uint64_t)W * Cin_p * 2, (uint64_t)H * W * Cin_p * 2};
+    uint32_t box[4] = {64, (uint32_t)a.BW, (uint32_t)a.BH, (uint32_t)a.BNi};
+    if (encode_tmap_bf16(&tmA, x, 4, dims, str, box)) return 1;
+  }
+  {
+    const uint64_t Ktot = (uint64_t)a.taps * Cin_p;
+    uint64_t dims[2] = {Ktot, (uint64_t)Np16};
+    uint64_t str[1] = {Ktot * 2};
+    uint32_t box[2] = {64, (uint32_t)n_tile};
+    if (encode_tmap_bf16(&tmB, wpack, 2, dims, str, box)) return 1;
+  }
+  const size_t smem = (size_t)stages * stage_bytes + 1024 + (2 * stages + 1) * 8 + 16;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  DTDL_CHECK_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set[dev & 63] = true;
+  }
+  dim3 grid(m_tiles, n_tiles);
+  conv_gemm_kernel<<<grid, 256, smem, stream>>>(tmA, tmB, a);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

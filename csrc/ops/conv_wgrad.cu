@@ -1,0 +1,300 @@
+// Weight-gradient of a stride-1 convolution / linear layer for sm_100a.
+//
+//   dw[co, ci, r, s] = sum_{n,ho,wo} dy[n,ho,wo,co] * x[n, ho+r-pad_h, wo+s-pad_w, ci]
+//
+// GEMM view: M = output channels (128 per CTA), N = input channels (64 per
+// CTA), K = pixels.  Both operands are "MN-major" for tcgen05 (channels are the
+// contiguous dimension of an NHWC tensor, the reduction runs over pixel rows),
+// so the TMA boxes [pixels][64 channels] that land in 128-byte-swizzled shared
+// memory are consumed as-is with the a_major/b_major bits set.  As in the
+// forward kernel the filter tap is a coordinate shift of the x box with the
+// zero padding supplied by the TMA unit.
+//
+// Work split: grid.x = pixel-range split (split-K), grid.y = (filter row,
+// group of <=3 filter columns), grid.z = (Cout tile, Cin chunk).  A CTA keeps
+// one 128x64 fp32 accumulator per filter column of its group in TMEM.
+// Partial sums go to a scratch workspace [split][tap][Cout_p][Cin_w] with plain
+// vector stores; dtdl_wgrad_reduce sums the splits in a fixed order (the
+// result is bitwise reproducible, unlike an atomic split-K) and writes the
+// fp32 gradient in the OIHW layout of the torch parameter.
+//
+// Capability covered: K-O4 / K-O12 of SURVEY.md section 2.5 (the reference
+// reaches cuDNN/cuBLAS through autograd of nn.Conv2d / nn.Linear:
+// pytorch/model.py:28-32,77; pytorch/single_gpu.py:102).
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+#include "../../include/dtdl_b200.h"
+
+namespace dtdl {
+
+void choose_pixel_tile(int N, int Ho, int Wo, int* BW, int* BH, int* BNi);
+
+struct WgradArgs {
+  int KW, pad_h, pad_w;
+  int groups_per_row;  // ceil(KW / 3)
+  int BW, BH, BNi, rows, kslices;
+  int tiles_w, tiles_h, tiles_n, n_ptiles;
+  int tiles_per_split;
+  int ci_chunks;
+  int m_boxes;  // 1 when Cout_p <= 64 (second dy box never loaded)
+  int Cout_p, Cin_w, taps;
+  int stages, stage_bytes;
+  int zero_fill;
+  float* ws;
+};
+
+static constexpr int kBox = 128 * 128;  // [128 pixel rows][64 bf16]
+
+__global__ void __launch_bounds__(256, 1)
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ CUtensorMap tmX,
+                  const WgradArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + a.stages * a.stage_bytes);
+  uint64_t* empty = full + a.stages;
+  uint64_t* tmem_full = empty + a.stages;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int split = blockIdx.x;
+  const int r = blockIdx.y / a.groups_per_row;
+  const int s0 = (blockIdx.y % a.groups_per_row) * 3;
+  const int ns = (a.KW - s0) < 3 ? (a.KW - s0) : 3;
+  const int co_tile = blockIdx.z / a.ci_chunks;
+  const int ci_chunk = blockIdx.z % a.ci_chunks;
+  const int co0 = co_tile * 128, ci0 = ci_chunk * 64;
+
+  const int pt_begin = split * a.tiles_per_split;
+  int pt_end = pt_begin + a.tiles_per_split;
+  if (pt_end > a.n_ptiles) pt_end = a.n_ptiles;
+  const int n_steps = pt_end - pt_begin;
+
+  if (a.zero_fill) {
+    // Pixel tiles with a row count that is not a multiple of 16 leave tail
+    // rows the TMA never writes; they are K padding and must read as zero.
+    uint4* p = reinterpret_cast<uint4*>(smem);
+    const int n16 = a.stages * a.stage_bytes / 16;
+    for (int i = threadIdx.x; i < n16; i += blockDim.x) p[i] = make_uint4(0, 0, 0, 0);
+    fence_proxy_async_smem();
+  }
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmDy);
+    tma_prefetch_desc(&tmX);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < a.stages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_ptr, 256);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      const uint32_t tx = (uint32_t)(a.rows * 128 * (a.m_boxes + ns));
+      int stage = 0, phase = 0;
+      for (int pt = pt_begin; pt < pt_end; ++pt) {
+        int t = pt;
+        const int w0 = (t % a.tiles_w) * a.BW;
+        t /= a.tiles_w;
+        const int h0 = (t % a.tiles_h) * a.BH;
+        const int n0 = (t / a.tiles_h) * a.BNi;
+        uint8_t* st = smem + stage * a.stage_bytes;
+        mbar_wait(&empty[stage], phase ^ 1, 11);
+        mbar_arrive_expect_tx(&full[stage], tx);
+        for (int b = 0; b < a.m_boxes; ++b)
+          tma_load_4d(st + b * kBox, &tmDy, &full[stage], co0 + b * 64, w0, h0, n0);
+        for (int s = 0; s < ns; ++s)
+          tma_load_4d(st + (2 + s) * kBox, &tmX, &full[stage], ci0, w0 + s0 + s - a.pad_w,
+                      h0 + r - a.pad_h, n0);
+        if (++stage == a.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      const uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);
+      const uint32_t base = smem_u32(smem);
+      int stage = 0, phase = 0;
+      for (int i = 0; i < n_steps; ++i) {
+        mbar_wait(&full[stage], phase, 12);
+        tc_fence_after();
+        const uint32_t st = base + stage * a.stage_bytes;
+        for (int s = 0; s < ns; ++s) {
+          for (int k = 0; k < a.kslices; ++k) {
+            const uint64_t ad = umma_smem_desc(st + k * 2048, kBox, 1024);
+            const uint64_t bd = umma_smem_desc(st + (2 + s) * kBox + k * 2048, kBox, 1024);
+            umma_bf16(tmem_base + s * 64, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          }
+        }
+        umma_commit(&empty[stage]);
+        if (++stage == a.stages) {
+          stage = 0;
+          phase ^= 1;
+        }
+      }
+      umma_commit(tmem_full);
+    }
+  } else if (warp >= 4) {
+    const int q = warp - 4;
+    const int co = co0 + q * 32 + lane;
+    const bool valid = co < a.Cout_p;
+    mbar_wait(tmem_full, 0, 13);
+    tc_fence_after();
+    const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+    for (int s = 0; s < ns; ++s) {
+      const int t = r * a.KW + s0 + s;
+      float* dst =
+          a.ws + (((size_t)split * a.taps + t) * a.Cout_p + (valid ? co : 0)) * a.Cin_w + ci0;
+      for (int j = 0; j < 4; ++j) {
+        uint32_t v[16];
+        tmem_ld16(lane_base + s * 64 + j * 16, v);
+        tmem_ld_wait();
+        if (valid) {
+          if (n_steps > 0) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              reinterpret_cast<uint4*>(dst + j * 16)[i] =
+                  make_uint4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              reinterpret_cast<uint4*>(dst + j * 16)[i] = make_uint4(0, 0, 0, 0);
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, 256);
+}
+
+// dw[co][ci][t] (OIHW, fp32) = (accumulate ? dw : 0) + sum_split ws[split][t][co][ci]
+__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw,
+                                    int splits, int taps, int Cout, int Cin, int Cout_p, int Cin_w,
+                                    int accumulate) {
+  const int ci = blockIdx.x * blockDim.x + threadIdx.x;
+  const int co = blockIdx.y;
+  if (ci >= Cin) return;
+  for (int t = 0; t < taps; ++t) {
+    float acc = 0.f;
+    const float* p = ws + ((size_t)t * Cout_p + co) * Cin_w + ci;
+    const size_t stride = (size_t)taps * Cout_p * Cin_w;
+    for (int s = 0; s < splits; ++s) acc += p[s * stride];
+    float* o = dw + ((size_t)co * Cin + ci) * taps + t;
+    *o = accumulate ? (*o + acc) : acc;
+  }
+}
+
+}  // namespace dtdl
+
+using namespace dtdl;
+
+// Plans the split-K decomposition; shared by the size query and the launch.
+static void wgrad_plan(int N, int Ho, int Wo, int Cin_p, int Cout_p, int KH, int KW, WgradArgs* a,
+                       int* splits) {
+  choose_pixel_tile(N, Ho, Wo, &a->BW, &a->BH, &a->BNi);
+  a->rows = a->BW * a->BH * a->BNi;
+  a->kslices = (a->rows + 15) / 16;
+  a->zero_fill = (a->rows % 16) != 0;
+  a->tiles_w = (Wo + a->BW - 1) / a->BW;
+  a->tiles_h = (Ho + a->BH - 1) / a->BH;
+  a->tiles_n = (N + a->BNi - 1) / a->BNi;
+  a->n_ptiles = a->tiles_w * a->tiles_h * a->tiles_n;
+  a->KW = KW;
+  a->groups_per_row = (KW + 2) / 3;
+  a->ci_chunks = (Cin_p + 63) / 64;
+  a->Cin_w = a->ci_chunks * 64;
+  a->Cout_p = Cout_p;
+  a->m_boxes = Cout_p <= 64 ? 1 : 2;
+  a->taps = KH * KW;
+  const int co_tiles = (Cout_p + 127) / 128;
+  const int groups = KH * a->groups_per_row * co_tiles * a->ci_chunks;
+  int sp = (2 * sm_count() + groups - 1) / groups;
+  if (sp > a->n_ptiles) sp = a->n_ptiles;
+  if (sp < 1) sp = 1;
+  a->tiles_per_split = (a->n_ptiles + sp - 1) / sp;
+  sp = (a->n_ptiles + a->tiles_per_split - 1) / a->tiles_per_split;
+  *splits = sp;
+}
+
+extern "C" long long dtdl_conv_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cin_p, int Cout_p,
+                                                     int KH, int KW) {
+  WgradArgs a;
+  int splits;
+  wgrad_plan(N, Ho, Wo, Cin_p, Cout_p, KH, KW, &a, &splits);
+  return (long long)splits * a.taps * Cout_p * a.Cin_w * 4;
+}
+
+extern "C" int dtdl_conv_wgrad(const void* x, const void* dy, float* dw, void* workspace,
+                               long long workspace_bytes, int N, int H, int W, int Cin, int Cin_p,
+                               int Ho, int Wo, int Cout, int Cout_p, int KH, int KW, int pad_h,
+                               int pad_w, int accumulate, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  DTDL_REQUIRE(Cin_p % 8 == 0 && Cout_p % 8 == 0, "channel counts must be padded to 8");
+  DTDL_REQUIRE(Ho == H + 2 * pad_h - KH + 1 && Wo == W + 2 * pad_w - KW + 1,
+               "output size does not match a stride-1 convolution");
+  WgradArgs a;
+  int splits;
+  wgrad_plan(N, Ho, Wo, Cin_p, Cout_p, KH, KW, &a, &splits);
+  a.pad_h = pad_h;
+  a.pad_w = pad_w;
+  const long long need = (long long)splits * a.taps * Cout_p * a.Cin_w * 4;
+  DTDL_REQUIRE(workspace != nullptr && workspace_bytes >= need,
+               "wgrad workspace too small (see dtdl_conv_wgrad_workspace_bytes)");
+  a.ws = reinterpret_cast<float*>(workspace);
+  a.stage_bytes = 5 * kBox;  // 2 dy boxes + 3 shifted x boxes
+  a.stages = 2;
+  const int steps = a.tiles_per_split;
+  if (steps < 2) a.stages = 1;
+
+  CUtensorMap tmDy, tmX;
+  {
+    uint64_t dims[4] = {(uint64_t)Cout_p, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)N};
+    uint64_t str[3] = {(uint64_t)Cout_p * 2, (uint64_t)Wo * Cout_p * 2,
+                       (uint64_t)Ho * Wo * Cout_p * 2};
+    uint32_t box[4] = {64, (uint32_t)a.BW, (uint32_t)a.BH, (uint32_t)a.BNi};
+    if (encode_tmap_bf16(&tmDy, dy, 4, dims, str, box)) return 1;
+  }
+  {
+    uint64_t dims[4] = {(uint64_t)Cin_p, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+    uint64_t str[3] = {(uint64_t)Cin_p * 2, (uint64_t)W * Cin_p * 2, (uint64_t)H * W * Cin_p * 2};
+    uint32_t box[4] = {64, (uint32_t)a.BW, (uint32_t)a.BH, (uint32_t)a.BNi};
+    if (encode_tmap_bf16(&tmX, x, 4, dims, str, box)) return 1;
+  }
+  const size_t smem = (size_t)a.stages * a.stage_bytes + 1024 + (2 * a.stages + 1) * 8 + 16;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  DTDL_CHECK_CUDA(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set[dev & 63] = true;
+  }
+  const int co_tiles = (Cout_p + 127) / 128;
+  dim3 grid(splits, KH * a.groups_per_row, co_tiles * a.ci_chunks);
+  conv_wgrad_kernel<<<grid, 256, smem, stream>>>(tmDy, tmX, a);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+
+  dim3 rgrid((Cin + 127) / 128, Cout);
+  wgrad_reduce_kernel<<<rgrid, 128, 0, stream>>>(a.ws, dw, splits, a.taps, Cout, Cin, Cout_p,
+                                                 a.Cin_w, accumulate);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

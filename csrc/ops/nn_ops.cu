@@ -1,0 +1,871 @@
+// Bandwidth-bound layer kernels on NHWC bf16 activations whose channel count is
+// padded to a multiple of 8 (one 16-byte vector = 8 channels of one pixel).
+// Pad channels are kept at exactly zero by every kernel here.
+//
+//   batch norm (train/eval) forward  : stats reduction + fused apply(+residual)(+ReLU)
+//   batch norm backward              : fused (ReLU mask) reduction + apply
+//   average / max pooling, 2x subsample, global average pool
+//   softmax cross entropy (loss, dlogits, correct count in one kernel)
+//   layout conversion NCHW fp32 -> NHWC bf16 (the source pointer may be peer memory)
+//
+// Capability covered: K-O5..K-O11, K-O13, K-O17, K-O19 of SURVEY.md section 2.5
+// (reference call sites: pytorch/model.py:10-20,27-34,40-50,74-76,107-111;
+// pytorch/single_gpu.py:99,105-108; tensorflow2/mnist_single.py:19-26).
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+#include "../../include/dtdl_b200.h"
+
+namespace dtdl {
+
+struct F8 {
+  float v[8];
+};
+__device__ __forceinline__ F8 unpack8(uint4 u) {
+  F8 r;
+  const __nv_bfloat162* p = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float2 f = __bfloat1622float2(p[i]);
+    r.v[2 * i] = f.x;
+    r.v[2 * i + 1] = f.y;
+  }
+  return r;
+}
+__device__ __forceinline__ uint4 pack8(const F8& f) {
+  uint4 u;
+  __nv_bfloat162* p = reinterpret_cast<__nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) p[i] = __floats2bfloat162_rn(f.v[2 * i], f.v[2 * i + 1]);
+  return u;
+}
+
+static inline int block_for_groups(int G) {
+  int b = G * (256 / G);
+  if (b < G) b = G;  // G > 256: one row of G threads (G <= 1024 is required)
+  return b;
+}
+static inline int grid_for(long long work_items, int per_block, int max_blocks) {
+  long long g = (work_items + per_block - 1) / per_block;
+  if (g > max_blocks) g = max_blocks;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+// ---------------------------------------------------------------------------
+// NCHW fp32 -> NHWC bf16 (channel padded).  One thread per (pixel, 8-channel group).
+// ---------------------------------------------------------------------------
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, uint4* __restrict__ y, int N, int C,
+                                    int HW, int G) {
+  const long long total = (long long)N * HW * G;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % G);
+    const long long pix = i / G;
+    const int hw = (int)(pix % HW);
+    const long long n = pix / HW;
+    F8 f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = g * 8 + k;
+      f.v[k] = c < C ? x[(n * C + c) * HW + hw] : 0.f;
+    }
+    y[i] = pack8(f);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Per-channel sum / sum of squares (accumulated with atomics into sums[2*Cp]).
+// ---------------------------------------------------------------------------
+__global__ void bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ sums, long long P,
+                                int G) {
+  extern __shared__ float red[];  // [rows][G][16]
+  const int rows = blockDim.x / G;
+  const int g = threadIdx.x % G, rrow = threadIdx.x / G;
+  float s1[8], s2[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+  for (long long p = (long long)blockIdx.x * rows + rrow; p < P; p += (long long)gridDim.x * rows) {
+    const F8 f = unpack8(x[p * G + g]);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      s1[k] += f.v[k];
+      s2[k] += f.v[k] * f.v[k];
+    }
+  }
+  float* mine = red + (size_t)threadIdx.x * 16;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    mine[k] = s1[k];
+    mine[8 + k] = s2[k];
+  }
+  __syncthreads();
+  // threads [0, G*16) each own one (g, k) pair and sum it over the rows
+  for (int o = threadIdx.x; o < G * 16; o += blockDim.x) {
+    const int og = o / 16, ok = o % 16;
+    float acc = 0.f;
+    for (int rr = 0; rr < rows; ++rr) acc += red[((size_t)rr * G + og) * 16 + ok];
+    const int Cp = G * 8;
+    if (ok < 8)
+      atomicAdd(&sums[og * 8 + ok], acc);
+    else
+      atomicAdd(&sums[Cp + og * 8 + (ok - 8)], acc);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// BN apply: y = [relu]( (x-mean)*rstd*gamma + beta [+ residual[..., :Cres_p]] )
+// training=1: mean/var from `sums`; block 0 also updates the running stats and
+// stores mean/rstd for backward.  training=0: mean/var from the running stats.
+// ---------------------------------------------------------------------------
+struct BnApplyArgs {
+  const uint4* x;
+  uint4* y;
+  const float* sums;
+  const float* gamma;
+  const float* beta;
+  float* running_mean;
+  float* running_var;
+  long long* num_batches_tracked;
+  float* save_mean;
+  float* save_rstd;
+  const uint4* residual;
+  int Gres;
+  long long P;
+  int C, G;
+  float eps, momentum;
+  int relu, training;
+  float* zero_buf;  // scratch of another pass that this launch resets (may be null)
+  int zero_n;
+};
+
+__global__ void bn_apply_kernel(const BnApplyArgs a) {
+  extern __shared__ float ss[];  // scale[Cp], shift[Cp]
+  const int Cp = a.G * 8;
+  float* sc = ss;
+  float* sh = ss + Cp;
+  for (int c = threadIdx.x; c < Cp; c += blockDim.x) {
+    float scale = 0.f, shift = 0.f;
+    if (c < a.C) {
+      float mean, var;
+      if (a.training) {
+        mean = a.sums[c] / (float)a.P;
+        var = fmaxf(a.sums[Cp + c] / (float)a.P - mean * mean, 0.f);
+      } else {
+        mean = a.running_mean[c];
+        var = a.running_var[c];
+      }
+      const float rstd = rsqrtf(var + a.eps);
+      scale = a.gamma[c] * rstd;
+      shift = a.beta[c] - mean * scale;
+      if (a.training && blockIdx.x == 0) {
+        a.save_mean[c] = mean;
+        a.save_rstd[c] = rstd;
+        if (a.running_mean != nullptr) {
+          const float unbiased = a.P > 1 ? var * (float)a.P / (float)(a.P - 1) : var;
+          a.running_mean[c] = (1.f - a.momentum) * a.running_mean[c] + a.momentum * mean;
+          a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * unbiased;
+        }
+      }
+    }
+    sc[c] = scale;
+    sh[c] = shift;
+  }
+  if (a.training && blockIdx.x == 0 && threadIdx.x == 0 && a.num_batches_tracked != nullptr)
+    *a.num_batches_tracked += 1;
+  if (blockIdx.x == 0 && a.zero_buf != nullptr)
+    for (int i = threadIdx.x; i < a.zero_n; i += blockDim.x) a.zero_buf[i] = 0.f;
+  __syncthreads();
+
+  const long long total = a.P * a.G;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % a.G);
+    const long long p = i / a.G;
+    F8 f = unpack8(a.x[i]);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f.v[k] = f.v[k] * sc[g * 8 + k] + sh[g * 8 + k];
+    if (a.residual != nullptr && g < a.Gres) {
+      const F8 r = unpack8(a.residual[p * a.Gres + g]);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f.v[k] += r.v[k];
+    }
+    if (a.relu) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f.v[k] = fmaxf(f.v[k], 0.f);
+    }
+    a.y[i] = pack8(f);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// BN backward, pass 1: sums2[c] = sum g, sums2[Cp+c] = sum g * xhat, g = dy*[y>0]
+// ---------------------------------------------------------------------------
+__global__ void bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x,
+                                     const uint4* __restrict__ y, const float* __restrict__ mean,
+                                     const float* __restrict__ rstd, float* __restrict__ sums2,
+                                     long long P, int C, int G, int relu) {
+  extern __shared__ float red[];
+  const int rows = blockDim.x / G;
+  const int g = threadIdx.x % G, rrow = threadIdx.x / G;
+  float m[8], rs[8], s1[8], s2[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = g * 8 + k;
+    m[k] = c < C ? mean[c] : 0.f;
+    rs[k] = c < C ? rstd[c] : 0.f;
+    s1[k] = s2[k] = 0.f;
+  }
+  for (long long p = (long long)blockIdx.x * rows + rrow; p < P; p += (long long)gridDim.x * rows) {
+    F8 d = unpack8(dy[p * G + g]);
+    const F8 xv = unpack8(x[p * G + g]);
+    if (relu) {
+      const F8 yv = unpack8(y[p * G + g]);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (!(yv.v[k] > 0.f)) d.v[k] = 0.f;
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      s1[k] += d.v[k];
+      s2[k] += d.v[k] * (xv.v[k] - m[k]) * rs[k];
+    }
+  }
+  float* mine = red + (size_t)threadIdx.x * 16;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    mine[k] = s1[k];
+    mine[8 + k] = s2[k];
+  }
+  __syncthreads();
+  for (int o = threadIdx.x; o < G * 16; o += blockDim.x) {
+    const int og = o / 16, ok = o % 16;
+    float acc = 0.f;
+    for (int rr = 0; rr < rows; ++rr) acc += red[((size_t)rr * G + og) * 16 + ok];
+    const int Cp = G * 8;
+    if (ok < 8)
+      atomicAdd(&sums2[og * 8 + ok], acc);
+    else
+      atomicAdd(&sums2[Cp + og * 8 + (ok - 8)], acc);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// BN backward, pass 2:
+//   dx = gamma*rstd*(g - sum_g/P - xhat*sum_gx/P);  dres = g[..., :Cres_p]
+//   dgamma = sum_gx, dbeta = sum_g  (block 0; written or accumulated)
+// ---------------------------------------------------------------------------
+struct BnBwdArgs {
+  const uint4* dy;
+  const uint4* x;
+  const uint4* y;
+  const float* mean;
+  const float* rstd;
+  const float* gamma;
+  const float* sums2;
+  uint4* dx;
+  uint4* dres;
+  int Gres;
+  float* dgamma;
+  float* dbeta;
+  int accumulate;
+  long long P;
+  int C, G, relu;
+  float* zero_buf;
+  int zero_n;
+};
+
+__global__ void bn_bwd_apply_kernel(const BnBwdArgs a) {
+  extern __shared__ float ss[];  // k1[Cp] = gamma*rstd, k2[Cp] = mean_g, k3[Cp] = mean_gx*rstd, m, rs
+  const int Cp = a.G * 8;
+  float* k1 = ss;
+  float* k2 = ss + Cp;
+  float* k3 = ss + 2 * Cp;
+  float* mm = ss + 3 * Cp;
+  float* rr = ss + 4 * Cp;
+  for (int c = threadIdx.x; c < Cp; c += blockDim.x) {
+    if (c < a.C) {
+      const float sg = a.sums2[c], sgx = a.sums2[Cp + c];
+      k1[c] = a.gamma[c] * a.rstd[c];
+      k2[c] = sg / (float)a.P;
+      k3[c] = sgx / (float)a.P;
+      mm[c] = a.mean[c];
+      rr[c] = a.rstd[c];
+      if (blockIdx.x == 0) {
+        if (a.accumulate) {
+          a.dgamma[c] += sgx;
+          a.dbeta[c] += sg;
+        } else {
+          a.dgamma[c] = sgx;
+          a.dbeta[c] = sg;
+        }
+      }
+    } else {
+      k1[c] = k2[c] = k3[c] = mm[c] = rr[c] = 0.f;
+    }
+  }
+  if (blockIdx.x == 0 && a.zero_buf != nullptr)
+    for (int i = threadIdx.x; i < a.zero_n; i += blockDim.x) a.zero_buf[i] = 0.f;
+  __syncthreads();
+  const long long total = a.P * a.G;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % a.G);
+    const long long p = i / a.G;
+    F8 d = unpack8(a.dy[i]);
+    const F8 xv = unpack8(a.x[i]);
+    if (a.relu) {
+      const F8 yv = unpack8(a.y[i]);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (!(yv.v[k] > 0.f)) d.v[k] = 0.f;
+    }
+    if (a.dres != nullptr && g < a.Gres) a.dres[p * a.Gres + g] = pack8(d);
+    F8 o;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = g * 8 + k;
+      const float xhat = (xv.v[k] - mm[c]) * rr[c];
+      o.v[k] = k1[c] * (d.v[k] - k2[c] - xhat * k3[c]);
+    }
+    a.dx[i] = pack8(o);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// relu backward on a saved output: dx = dy * [y > 0]
+// ---------------------------------------------------------------------------
+__global__ void relu_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
+                                uint4* __restrict__ dx, long long n16) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16;
+       i += (long long)gridDim.x * blockDim.x) {
+    F8 d = unpack8(dy[i]);
+    const F8 yv = unpack8(y[i]);
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (!(yv.v[k] > 0.f)) d.v[k] = 0.f;
+    dx[i] = pack8(d);
+  }
+}
+
+// out = a + b  (bf16 vectors)
+__global__ void add_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b,
+                           uint4* __restrict__ o, long long n16) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16;
+       i += (long long)gridDim.x * blockDim.x) {
+    F8 x = unpack8(a[i]);
+    const F8 y = unpack8(b[i]);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) x.v[k] += y.v[k];
+    o[i] = pack8(x);
+  }
+}
+
+// a[..., :Gb] += b  (channel-prefix add: the gradient of PyramidNet's zero-padded shortcut)
+__global__ void add_prefix_kernel(uint4* __restrict__ a, const uint4* __restrict__ b, long long P,
+                                  int Ga, int Gb) {
+  const long long total = P * Gb;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % Gb);
+    const long long p = i / Gb;
+    F8 x = unpack8(a[p * Ga + g]);
+    const F8 y = unpack8(b[i]);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) x.v[k] += y.v[k];
+    a[p * Ga + g] = pack8(x);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Pooling on NHWC.  mode 0 = average (count includes only in-bounds taps when
+// ceil-mode windows overhang; the reference's AvgPool2d(2, stride=2,
+// ceil_mode=True) on even sizes never overhangs), mode 1 = max.
+// ---------------------------------------------------------------------------
+__global__ void pool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int N, int H,
+                                int W, int Ho, int Wo, int G, int k, int stride, int pad, int mode) {
+  const long long total = (long long)N * Ho * Wo * G;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % G);
+    long long t = i / G;
+    const int wo = (int)(t % Wo);
+    t /= Wo;
+    const int ho = (int)(t % Ho);
+    const long long n = t / Ho;
+    F8 acc;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) acc.v[q] = mode ? -3.0e38f : 0.f;
+    int cnt = 0;
+    for (int r = 0; r < k; ++r) {
+      const int h = ho * stride - pad + r;
+      if (h < 0 || h >= H) continue;
+      for (int s = 0; s < k; ++s) {
+        const int w = wo * stride - pad + s;
+        if (w < 0 || w >= W) continue;
+        const F8 v = unpack8(x[((n * H + h) * W + w) * G + g]);
+        ++cnt;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) acc.v[q] = mode ? fmaxf(acc.v[q], v.v[q]) : acc.v[q] + v.v[q];
+      }
+    }
+    if (!mode) {
+      const float inv = cnt > 0 ? 1.f / (float)cnt : 0.f;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) acc.v[q] *= inv;
+    }
+    y[i] = pack8(acc);
+  }
+}
+
+// Gather-form backward (no atomics): each input element sums the windows it belongs to.
+__global__ void pool_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x,
+                                const uint4* __restrict__ y, uint4* __restrict__ dx, int N, int H,
+                                int W, int Ho, int Wo, int G, int k, int stride, int pad, int mode) {
+  const long long total = (long long)N * H * W * G;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % G);
+    long long t = i / G;
+    const int w = (int)(t % W);
+    t /= W;
+    const int h = (int)(t % H);
+    const long long n = t / H;
+    F8 acc;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) acc.v[q] = 0.f;
+    F8 xv;
+    if (mode) xv = unpack8(x[i]);
+    for (int ho = 0; ho < Ho; ++ho) {
+      const int r = h - (ho * stride - pad);
+      if (r < 0 || r >= k) continue;
+      for (int wo = 0; wo < Wo; ++wo) {
+        const int s = w - (wo * stride - pad);
+        if (s < 0 || s >= k) continue;
+        const long long oi = ((n * Ho + ho) * Wo + wo) * G + g;
+        const F8 d = unpack8(dy[oi]);
+        if (mode) {
+          const F8 yv = unpack8(y[oi]);
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            if (xv.v[q] == yv.v[q]) acc.v[q] += d.v[q];
+        } else {
+          int hs = ho * stride - pad, ws = wo * stride - pad;
+          int he = hs + k < H ? hs + k : H, we = ws + k < W ? ws + k : W;
+          hs = hs < 0 ? 0 : hs;
+          ws = ws < 0 ? 0 : ws;
+          const float inv = 1.f / (float)((he - hs) * (we - ws));
+#pragma unroll
+          for (int q = 0; q < 8; ++q) acc.v[q] += d.v[q] * inv;
+        }
+      }
+    }
+    dx[i] = pack8(acc);
+  }
+}
+
+// y[n,ho,wo] = x[n, 2ho, 2wo]   and its adjoint (zero insertion)
+__global__ void subsample2_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int N, int H,
+                                  int W, int Ho, int Wo, int G, int adjoint) {
+  if (!adjoint) {
+    const long long total = (long long)N * Ho * Wo * G;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+      const int g = (int)(i % G);
+      long long t = i / G;
+      const int wo = (int)(t % Wo);
+      t /= Wo;
+      const int ho = (int)(t % Ho);
+      const long long n = t / Ho;
+      y[i] = x[((n * H + 2 * ho) * W + 2 * wo) * G + g];
+    }
+  } else {
+    // here x is the small [N,Ho,Wo] gradient and y the big [N,H,W] one
+    const long long total = (long long)N * H * W * G;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+      const int g = (int)(i % G);
+      long long t = i / G;
+      const int w = (int)(t % W);
+      t /= W;
+      const int h = (int)(t % H);
+      const long long n = t / H;
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if ((h & 1) == 0 && (w & 1) == 0 && h / 2 < Ho && w / 2 < Wo)
+        v = x[((n * Ho + h / 2) * Wo + w / 2) * G + g];
+      y[i] = v;
+    }
+  }
+}
+
+// Global average pool [N,HW,Cp] -> [N,Cp] and its backward (broadcast / HW).
+__global__ void gap_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int N, int HW,
+                               int G) {
+  const long long total = (long long)N * G;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % G);
+    const long long n = i / G;
+    F8 acc;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) acc.v[q] = 0.f;
+    for (int p = 0; p < HW; ++p) {
+      const F8 v = unpack8(x[(n * HW + p) * G + g]);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) acc.v[q] += v.v[q];
+    }
+    const float inv = 1.f / (float)HW;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) acc.v[q] *= inv;
+    y[i] = pack8(acc);
+  }
+}
+__global__ void gap_bwd_kernel(const uint4* __restrict__ dy, uint4* __restrict__ dx, int N, int HW,
+                               int G) {
+  const long long total = (long long)N * HW * G;
+  const float inv = 1.f / (float)HW;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % G);
+    const long long n = i / ((long long)HW * G);
+    F8 d = unpack8(dy[n * G + g]);
+#pragma unroll
+    for (int q = 0; q < 8; ++q) d.v[q] *= inv;
+    dx[i] = pack8(d);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Softmax cross entropy (mean over the batch).  One warp per sample.
+//   out[0] += loss_n / N_total      out[1] += [argmax == target]
+//   dlogits[n, c] = (softmax - onehot) * grad_scale        (bf16, pad channels 0)
+// probs_input=1 treats `logits` as probabilities (Keras' softmax-in-model +
+// sparse_categorical_crossentropy pairing, tensorflow2/mnist_single.py:26,79).
+// ---------------------------------------------------------------------------
+__global__ void softmax_ce_kernel(const float* __restrict__ logits, const long long* __restrict__ tgt,
+                                  float* __restrict__ out, __nv_bfloat16* __restrict__ dlogits,
+                                  float* __restrict__ dlogits_f32, int N, int C, int Cp,
+                                  float inv_n, float grad_scale) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (warp >= N) return;
+  const float* row = logits + (size_t)warp * Cp;
+  float mx = -3.0e38f;
+  int am = 0;
+  for (int c = lane; c < C; c += 32) {
+    const float v = row[c];
+    if (v > mx) {
+      mx = v;
+      am = c;
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const float omx = __shfl_xor_sync(0xffffffffu, mx, o);
+    const int oam = __shfl_xor_sync(0xffffffffu, am, o);
+    if (omx > mx || (omx == mx && oam < am)) {
+      mx = omx;
+      am = oam;
+    }
+  }
+  float se = 0.f;
+  for (int c = lane; c < C; c += 32) se += __expf(row[c] - mx);
+  for (int o = 16; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o);
+  const int t = (int)tgt[warp];
+  const float lse = mx + __logf(se);
+  if (lane == 0) {
+    atomicAdd(&out[0], (lse - row[t]) * inv_n);
+    if (am == t) atomicAdd(&out[1], 1.f);
+  }
+  for (int c = lane; c < Cp; c += 32) {
+    float gval = 0.f;
+    if (c < C) gval = (__expf(row[c] - lse) - (c == t ? 1.f : 0.f)) * grad_scale;
+    if (dlogits != nullptr) dlogits[(size_t)warp * Cp + c] = __float2bfloat16(gval);
+    if (dlogits_f32 != nullptr) dlogits_f32[(size_t)warp * Cp + c] = gval;
+  }
+}
+
+// Column sum of a bf16 [P][Cp] matrix into fp32 out[C] (bias gradients).
+__global__ void colsum_kernel(const uint4* __restrict__ x, float* __restrict__ out, long long P,
+                              int C, int G) {
+  extern __shared__ float red[];  // [rows][G][8]
+  const int rows = blockDim.x / G;
+  const int g = threadIdx.x % G, rrow = threadIdx.x / G;
+  float s[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = 0.f;
+  for (long long p = (long long)blockIdx.x * rows + rrow; p < P; p += (long long)gridDim.x * rows) {
+    const F8 f = unpack8(x[p * G + g]);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s[k] += f.v[k];
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) red[(size_t)threadIdx.x * 8 + k] = s[k];
+  __syncthreads();
+  for (int o = threadIdx.x; o < G * 8; o += blockDim.x) {
+    const int og = o / 8, ok = o % 8;
+    float acc = 0.f;
+    for (int rr = 0; rr < rows; ++rr) acc += red[((size_t)rr * G + og) * 8 + ok];
+    if (og * 8 + ok < C) atomicAdd(&out[og * 8 + ok], acc);
+  }
+}
+
+// fp32 [rows][cols] -> bf16 [rows][cols_p] (zero padded) and back
+__global__ void f32_to_bf16_pad_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y,
+                                       long long rows, int cols, int cols_p) {
+  const long long total = rows * cols_p;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cols_p);
+    const long long r = i / cols_p;
+    y[i] = __float2bfloat16(c < cols ? x[r * cols + c] : 0.f);
+  }
+}
+__global__ void bf16_to_f32_unpad_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ y,
+                                         long long rows, int cols, int cols_p) {
+  const long long total = rows * cols;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % cols);
+    const long long r = i / cols;
+    y[i] = __bfloat162float(x[r * cols_p + c]);
+  }
+}
+
+}  // namespace dtdl
+
+using namespace dtdl;
+#define STREAM(s) reinterpret_cast<cudaStream_t>(s)
+static const int kMaxBlocks = 148 * 8;
+
+extern "C" int dtdl_nchw_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, int Cp,
+                                      void* stream) {
+  DTDL_REQUIRE(Cp % 8 == 0 && Cp >= C, "bad channel padding");
+  const int G = Cp / 8;
+  const long long total = (long long)N * H * W * G;
+  nchw_to_nhwc_kernel<<<grid_for(total, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
+      x, reinterpret_cast<uint4*>(y), N, C, H * W, G);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_bn_stats(const void* x, float* sums, long long P, int Cp, void* stream) {
+  DTDL_REQUIRE(Cp % 8 == 0 && Cp <= 8192, "bad channel padding");
+  const int G = Cp / 8;
+  const int block = block_for_groups(G);
+  const int rows = block / G;
+  const size_t smem = (size_t)block * 16 * sizeof(float);
+  static bool attr[64] = {false};
+  int dev = 0;
+  DTDL_CHECK_CUDA(cudaGetDevice(&dev));
+  if (!attr[dev & 63]) {
+    DTDL_CHECK_CUDA(
+        cudaFuncSetAttribute(bn_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(bn_bwd_reduce_kernel,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+    attr[dev & 63] = true;
+  }
+  bn_stats_kernel<<<grid_for(P, rows * 8, 148 * 4), block, smem, STREAM(stream)>>>(
+      reinterpret_cast<const uint4*>(x), sums, P, G);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_bn_apply(const void* x, void* y, const float* sums, const float* gamma,
+                             const float* beta, float* running_mean, float* running_var,
+                             long long* num_batches_tracked, float* save_mean, float* save_rstd,
+                             const void* residual, int Cres_p, long long P, int C, int Cp, float eps,
+                             float momentum, int relu, int training, float* zero_buf, int zero_n,
+                             void* stream) {
+  DTDL_REQUIRE(Cp % 8 == 0 && Cres_p % 8 == 0 && Cres_p <= Cp, "bad channel padding");
+  BnApplyArgs a;
+  a.x = reinterpret_cast<const uint4*>(x);
+  a.y = reinterpret_cast<uint4*>(y);
+  a.sums = sums;
+  a.gamma = gamma;
+  a.beta = beta;
+  a.running_mean = running_mean;
+  a.running_var = running_var;
+  a.num_batches_tracked = num_batches_tracked;
+  a.save_mean = save_mean;
+  a.save_rstd = save_rstd;
+  a.residual = reinterpret_cast<const uint4*>(residual);
+  a.Gres = Cres_p / 8;
+  a.P = P;
+  a.C = C;
+  a.G = Cp / 8;
+  a.eps = eps;
+  a.momentum = momentum;
+  a.relu = relu;
+  a.training = training;
+  a.zero_buf = zero_buf;
+  a.zero_n = zero_n;
+  const long long total = P * a.G;
+  bn_apply_kernel<<<grid_for(total, 256 * 4, kMaxBlocks), 256, 2 * Cp * sizeof(float),
+                    STREAM(stream)>>>(a);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_bn_bwd(const void* dy, const void* x, const void* y, const float* save_mean,
+                           const float* save_rstd, const float* gamma, float* sums2, void* dx,
+                           void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
+                           long long P, int C, int Cp, int relu, float* zero_buf, int zero_n,
+                           void* stream) {
+  DTDL_REQUIRE(Cp % 8 == 0 && Cres_p % 8 == 0 && Cres_p <= Cp && Cp <= 8192, "bad channel padding");
+  DTDL_REQUIRE(!relu || y != nullptr, "relu backward needs the saved output");
+  const int G = Cp / 8;
+  {
+    const int block = block_for_groups(G);
+    const int rows = block / G;
+    const size_t smem = (size_t)block * 16 * sizeof(float);
+    bn_bwd_reduce_kernel<<<grid_for(P, rows * 8, 148 * 4), block, smem, STREAM(stream)>>>(
+        reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(x),
+        reinterpret_cast<const uint4*>(y), save_mean, save_rstd, sums2, P, C, G, relu);
+    DTDL_CHECK_CUDA(cudaGetLastError());
+  }
+  BnBwdArgs a;
+  a.dy = reinterpret_cast<const uint4*>(dy);
+  a.x = reinterpret_cast<const uint4*>(x);
+  a.y = reinterpret_cast<const uint4*>(y);
+  a.mean = save_mean;
+  a.rstd = save_rstd;
+  a.gamma = gamma;
+  a.sums2 = sums2;
+  a.dx = reinterpret_cast<uint4*>(dx);
+  a.dres = reinterpret_cast<uint4*>(dres);
+  a.Gres = Cres_p / 8;
+  a.dgamma = dgamma;
+  a.dbeta = dbeta;
+  a.accumulate = accumulate;
+  a.P = P;
+  a.C = C;
+  a.G = G;
+  a.relu = relu;
+  a.zero_buf = zero_buf;
+  a.zero_n = zero_n;
+  const long long total = P * G;
+  bn_bwd_apply_kernel<<<grid_for(total, 256 * 4, kMaxBlocks), 256, 5 * Cp * sizeof(float),
+                        STREAM(stream)>>>(a);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_relu_bwd(const void* dy, const void* y, void* dx, long long n_elems,
+                             void* stream) {
+  DTDL_REQUIRE(n_elems % 8 == 0, "element count must be a multiple of 8");
+  const long long n16 = n_elems / 8;
+  relu_bwd_kernel<<<grid_for(n16, 256 * 4, kMaxBlocks), 256, 0, STREAM(stream)>>>(
+      reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),
+      reinterpret_cast<uint4*>(dx), n16);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_add_bf16(const void* a, const void* b, void* out, long long n_elems,
+                             void* stream) {
+  DTDL_REQUIRE(n_elems % 8 == 0, "element count must be a multiple of 8");
+  const long long n16 = n_elems / 8;
+  add_kernel<<<grid_for(n16, 256 * 4, kMaxBlocks), 256, 0, STREAM(stream)>>>(
+      reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b),
+      reinterpret_cast<uint4*>(out), n16);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_add_prefix_bf16(void* a, const void* b, long long P, int Ca_p, int Cb_p,
+                                    void* stream) {
+  DTDL_REQUIRE(Ca_p % 8 == 0 && Cb_p % 8 == 0 && Cb_p <= Ca_p, "bad channel padding");
+  add_prefix_kernel<<<grid_for(P * (Cb_p / 8), 256 * 4, kMaxBlocks), 256, 0, STREAM(stream)>>>(
+      reinterpret_cast<uint4*>(a), reinterpret_cast<const uint4*>(b), P, Ca_p / 8, Cb_p / 8);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_pool_fwd(const void* x, void* y, int N, int H, int W, int Ho, int Wo, int Cp,
+                             int k, int stride, int pad, int mode, void* stream) {
+  DTDL_REQUIRE(Cp % 8 == 0, "bad channel padding");
+  const long long total = (long long)N * Ho * Wo * (Cp / 8);
+  pool_fwd_kernel<<<grid_for(total, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
+      reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(y), N, H, W, Ho, Wo, Cp / 8, k,
+      stride, pad, mode);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_pool_bwd(const void* dy, const void* x, const void* y, void* dx, int N, int H,
+                             int W, int Ho, int Wo, int Cp, int k, int stride, int pad, int mode,
+                             void* stream) {
+  DTDL_REQUIRE(Cp % 8 == 0, "bad channel padding");
+  const long long total = (long long)N * H * W * (Cp / 8);
+  pool_bwd_kernel<<<grid_for(total, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
+      reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(x),
+      reinterpret_cast<const uint4*>(y), reinterpret_cast<uint4*>(dx), N, H, W, Ho, Wo, Cp / 8, k,
+      stride, pad, mode);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_subsample2(const void* x, void* y, int N, int H, int W, int Cp, int adjoint,
+                               void* stream) {
+  DTDL_REQUIRE(Cp % 8 == 0, "bad channel padding");
+  const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
+  const long long total = (long long)N * (adjoint ? H * W : Ho * Wo) * (Cp / 8);
+  subsample2_kernel<<<grid_for(total, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
+      reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(y), N, H, W, Ho, Wo, Cp / 8,
+      adjoint);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_gap_fwd(const void* x, void* y, int N, int HW, int Cp, void* stream) {
+  DTDL_REQUIRE(Cp % 8 == 0, "bad channel padding");
+  gap_fwd_kernel<<<grid_for((long long)N * (Cp / 8), 64, kMaxBlocks), 64, 0, STREAM(stream)>>>(
+      reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(y), N, HW, Cp / 8);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int dtdl_gap_bwd(const void* dy, void* dx, int N, int HW, int Cp, void* stream) {
+  DTDL_REQUIRE(Cp % 8 == 0, "bad channel padding");
+  gap_bwd_kernel<<<grid_for((long long)N * HW * (Cp / 8), 256, kMaxBlocks), 256, 0,
+                   STREAM(stream)>>>(reinterpret_cast<const uint4*>(dy),
+                                     reinterpret_cast<uint4*>(dx), N, HW, Cp / 8);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_softmax_ce(const float* logits, const long long* targets, float* out2,
+                               void* dlogits_bf16, float* dlogits_f32, int N, int C, int Cp,
+                               float inv_n, float grad_scale, void* stream) {
+  const int warps_per_block = 4;
+  softmax_ce_kernel<<<(N + warps_per_block - 1) / warps_per_block, warps_per_block * 32, 0,
+                      STREAM(stream)>>>(logits, targets, out2,
+                                        reinterpret_cast<__nv_bfloat16*>(dlogits_bf16), dlogits_f32,
+                                        N, C, Cp, inv_n, grad_scale);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_colsum(const void* x, float* out, long long P, int C, int Cp, void* stream) {
+  DTDL_REQUIRE(Cp % 8 == 0 && Cp <= 8192, "bad channel padding");
+  const int G = Cp / 8;
+  const int block = block_for_groups(G);
+  const int rows = block / G;
+  colsum_kernel<<<grid_for(P, rows * 8, 148 * 2), block, (size_t)block * 8 * sizeof(float),
+                  STREAM(stream)>>>(reinterpret_cast<const uint4*>(x), out, P, C, G);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_f32_to_bf16_pad(const float* x, void* y, long long rows, int cols, int cols_p,
+                                    void* stream) {
+  f32_to_bf16_pad_kernel<<<grid_for(rows * cols_p, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
+      x, reinterpret_cast<__nv_bfloat16*>(y), rows, cols, cols_p);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int dtdl_bf16_to_f32_unpad(const void* x, float* y, long long rows, int cols, int cols_p,
+                                      void* stream) {
+  bf16_to_f32_unpad_kernel<<<grid_for(rows * cols, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(x), y, rows, cols, cols_p);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

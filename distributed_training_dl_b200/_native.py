@@ -1,0 +1,114 @@
+"""ctypes binding of ``libdtdl_b200.so`` (the sm_100a kernels + peer-memory runtime).
+
+The prototypes are read from ``include/dtdl_b200.h`` so Python and C cannot drift
+apart.  The library is built in-tree by ``build.sh`` / ``__graft_entry__.build()``.
+On a machine with a GPU a missing library is a hard error: the CUDA path must be
+the one that runs, never a silent PyTorch fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import re
+import subprocess
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_ROOT = os.path.dirname(_HERE)
+LIB_PATH = os.path.join(_HERE, "lib", "libdtdl_b200.so")
+HEADER_PATH = os.path.join(_ROOT, "include", "dtdl_b200.h")
+
+_lock = threading.Lock()
+_lib = None
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+_CTYPE = {
+    "int": ctypes.c_int,
+    "long long": ctypes.c_longlong,
+    "float": ctypes.c_float,
+}
+
+
+def _parse_header(path):
+    """Returns {name: (restype, [argtypes])} for every prototype in the header."""
+    src = open(path).read()
+    src = re.sub(r"/\*.*?\*/", " ", src, flags=re.S)
+    protos = {}
+    for m in re.finditer(r"\b(const char\*|int|long long)\s+(dtdl_\w+)\s*\(([^;]*?)\)\s*;", src, flags=re.S):
+        ret, name, args = m.group(1), m.group(2), m.group(3)
+        restype = ctypes.c_char_p if ret == "const char*" else _CTYPE[ret]
+        argtypes = []
+        args = " ".join(args.split())
+        if args and args != "void":
+            for a in args.split(","):
+                a = a.strip()
+                if "*" in a:
+                    argtypes.append(ctypes.c_void_p)
+                else:
+                    base = "long long" if a.startswith("long long") else a.split()[0]
+                    argtypes.append(_CTYPE[base])
+        protos[name] = (restype, argtypes)
+    return protos
+
+
+def build(verbose=False):
+    """Compile the library in-tree (nvcc cross-compiles for sm_100a without a GPU)."""
+    script = os.path.join(_ROOT, "build.sh")
+    res = subprocess.run(["bash", script], cwd=_ROOT, capture_output=True, text=True)
+    if verbose or res.returncode != 0:
+        print(res.stdout)
+        print(res.stderr)
+    if res.returncode != 0:
+        raise NativeError("building libdtdl_b200.so failed:\n" + res.stdout + res.stderr)
+    return LIB_PATH
+
+
+def available():
+    return os.path.exists(LIB_PATH)
+
+
+def lib():
+    """Loads (once) and returns the ctypes library handle with typed prototypes."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    with _lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(LIB_PATH):
+            raise NativeError(
+                f"{LIB_PATH} is missing; run ./build.sh (or __graft_entry__.build()) first. "
+                "The framework does not fall back to PyTorch kernels on a GPU.")
+        handle = ctypes.CDLL(LIB_PATH, mode=ctypes.RTLD_GLOBAL)
+        for name, (restype, argtypes) in _parse_header(HEADER_PATH).items():
+            fn = getattr(handle, name)
+            fn.restype = restype
+            fn.argtypes = argtypes
+        _lib = handle
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        msg = lib().dtdl_last_error()
+        raise NativeError(msg.decode() if msg else f"native call failed with code {rc}")
+
+
+def call(name, *args):
+    """Calls ``dtdl_<name>`` and raises NativeError on a non-zero return code."""
+    fn = getattr(lib(), "dtdl_" + name)
+    check(fn(*args))
+
+
+def ptr(t):
+    """Device pointer of a tensor (or 0 for None) as an int usable for c_void_p."""
+    return 0 if t is None else t.data_ptr()
+
+
+def stream_ptr():
+    import torch
+    return torch.cuda.current_stream().cuda_stream

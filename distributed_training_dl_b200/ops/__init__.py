@@ -1,0 +1,6 @@
+from . import functional
+from .modules import (AvgPool2d, BatchNorm2d, Conv2d, Flatten, GlobalAvgPool2d, InputLayout, Linear,
+                      MaxPool2d, OutputLayout, pack_weights, packed_layers)
+
+__all__ = ["functional", "AvgPool2d", "BatchNorm2d", "Conv2d", "Flatten", "GlobalAvgPool2d",
+           "InputLayout", "Linear", "MaxPool2d", "OutputLayout", "pack_weights", "packed_layers"]

@@ -1,0 +1,407 @@
+"""Autograd functions over the sm_100a kernels.
+
+Activation layout on the GPU: NHWC bf16, channel count padded to a multiple of 8
+(``Cp``), pad channels exactly zero.  A 2-D activation (Linear) is ``[N,1,1,Cp]``.
+Parameter gradients are written by the kernels straight into the parameter's
+gradient buffer (a view of the reducer's flat arena when the model is wrapped),
+so autograd never materialises or accumulates a weight gradient itself.
+"""
+from __future__ import annotations
+
+import torch
+
+from .. import _native as nv
+
+
+def pad8(c: int) -> int:
+    return (c + 7) // 8 * 8
+
+
+def pad16(c: int) -> int:
+    return (c + 15) // 16 * 16
+
+
+# --------------------------------------------------------------------------------------
+# gradient buffers
+# --------------------------------------------------------------------------------------
+def grad_buffer(p: torch.Tensor):
+    """Returns (fp32 gradient tensor of ``p``, accumulate flag) for a kernel to write into.
+
+    * wrapped model: ``p._dtdl_grad`` is a view of the flat gradient arena;
+    * bare module:   the buffer is created on first use.
+
+    ``accumulate`` is 0 for the first write after ``zero_grad`` and 1 afterwards, which
+    reproduces torch's "grads add up until zeroed" contract without a memset.
+    """
+    g = getattr(p, "_dtdl_grad", None)
+    if g is None:
+        g = torch.zeros_like(p, dtype=torch.float32, memory_format=torch.contiguous_format)
+        p._dtdl_grad = g
+    fresh = p.grad is None or getattr(p, "_dtdl_fresh", False)
+    if p.grad is not g:
+        p.grad = g
+    p._dtdl_fresh = False
+    return g, (0 if fresh else 1)
+
+
+def mark_fresh(params):
+    """``zero_grad`` without touching memory: the next backward overwrites."""
+    for p in params:
+        p._dtdl_fresh = True
+
+
+_ready_hooks = []
+
+
+def add_ready_hook(fn):
+    """``fn(param)`` is called when a kernel has enqueued the final gradient of ``param``."""
+    _ready_hooks.append(fn)
+    return fn
+
+
+def remove_ready_hook(fn):
+    if fn in _ready_hooks:
+        _ready_hooks.remove(fn)
+
+
+def _grad_ready(p):
+    for fn in _ready_hooks:
+        fn(p)
+
+
+# --------------------------------------------------------------------------------------
+# scratch
+# --------------------------------------------------------------------------------------
+_scratch = {}
+
+
+def scratch(device, nbytes: int) -> torch.Tensor:
+    """Per-device scratch buffer, grown on demand (stream-ordered reuse)."""
+    key = (device.type, device.index)
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < nbytes:
+        nbytes = max(nbytes, 32 << 20)
+        buf = torch.empty(nbytes, dtype=torch.uint8, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+# --------------------------------------------------------------------------------------
+# layout
+# --------------------------------------------------------------------------------------
+def to_nhwc(x: torch.Tensor, Cp: int | None = None) -> torch.Tensor:
+    """NCHW (or [N,F]) fp32 -> NHWC bf16 padded.  No gradient flows to the input."""
+    if x.dim() == 2:
+        N, C = x.shape
+        Cp = Cp or pad8(C)
+        y = torch.empty((N, 1, 1, Cp), dtype=torch.bfloat16, device=x.device)
+        nv.call("f32_to_bf16_pad", nv.ptr(x.contiguous().float()), nv.ptr(y), N, C, Cp, nv.stream_ptr())
+        return y
+    N, C, H, W = x.shape
+    Cp = Cp or pad8(C)
+    x = x.detach()
+    if x.dtype != torch.float32 or not x.is_contiguous():
+        x = x.contiguous().float()
+    y = torch.empty((N, H, W, Cp), dtype=torch.bfloat16, device=x.device)
+    nv.call("nchw_to_nhwc_bf16", nv.ptr(x), nv.ptr(y), N, C, H, W, Cp, nv.stream_ptr())
+    return y
+
+
+class _ToF32(torch.autograd.Function):
+    """[N,1,1,Cp] bf16 -> [N,C] fp32 (e.g. logits handed to a user criterion)."""
+
+    @staticmethod
+    def forward(ctx, x, C):
+        N, Cp = x.shape[0], x.shape[-1]
+        ctx.meta = (N, C, Cp)
+        y = torch.empty((N, C), dtype=torch.float32, device=x.device)
+        nv.call("bf16_to_f32_unpad", nv.ptr(x), nv.ptr(y), N, C, Cp, nv.stream_ptr())
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        N, C, Cp = ctx.meta
+        dy = dy.contiguous().float()
+        dx = torch.empty((N, 1, 1, Cp), dtype=torch.bfloat16, device=dy.device)
+        nv.call("f32_to_bf16_pad", nv.ptr(dy), nv.ptr(dx), N, C, Cp, nv.stream_ptr())
+        return dx, None
+
+
+def to_f32(x, C):
+    return _ToF32.apply(x, C)
+
+
+# --------------------------------------------------------------------------------------
+# convolution / linear
+# --------------------------------------------------------------------------------------
+def _conv_out(n, k, pad):
+    return n + 2 * pad - k + 1
+
+
+def conv_fprop_raw(x, wpack, Cout_p, KH, KW, pad, bias=None, relu=False, out_f32=False):
+    N, H, W, Cin_p = x.shape
+    Ho, Wo = _conv_out(H, KH, pad), _conv_out(W, KW, pad)
+    y = torch.empty((N, Ho, Wo, Cout_p), dtype=torch.float32 if out_f32 else torch.bfloat16,
+                    device=x.device)
+    flags = (1 if relu else 0) | (2 if out_f32 else 0)
+    nv.call("conv_fprop", nv.ptr(x), nv.ptr(wpack), nv.ptr(y), nv.ptr(bias), N, H, W, Cin_p, Ho, Wo,
+            Cout_p, KH, KW, pad, pad, flags, nv.stream_ptr())
+    return y
+
+
+def subsample2_raw(x, adjoint=False, full_hw=None):
+    if not adjoint:
+        N, H, W, Cp = x.shape
+        y = torch.empty((N, (H + 1) // 2, (W + 1) // 2, Cp), dtype=x.dtype, device=x.device)
+        nv.call("subsample2", nv.ptr(x), nv.ptr(y), N, H, W, Cp, 0, nv.stream_ptr())
+        return y
+    N, _, _, Cp = x.shape
+    H, W = full_hw
+    y = torch.empty((N, H, W, Cp), dtype=x.dtype, device=x.device)
+    nv.call("subsample2", nv.ptr(x), nv.ptr(y), N, H, W, Cp, 1, nv.stream_ptr())
+    return y
+
+
+class _Conv(torch.autograd.Function):
+    """Convolution (stride 1 or 2) / Linear with optional fused bias + ReLU epilogue.
+
+    Stride 2 is the stride-1 kernel followed by a 2x subsample (two layers of PyramidNet,
+    three of ResNet-50); its backward zero-inserts dy and reuses the stride-1 kernels.
+    """
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, mod):
+        x = x.contiguous()
+        y = conv_fprop_raw(x, mod.wf, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad, bias=bias,
+                           relu=mod.fuse_relu, out_f32=False)
+        full_hw = (y.shape[1], y.shape[2])
+        if mod.conv_stride == 2:
+            y = subsample2_raw(y)
+        ctx.mod = mod
+        ctx.full_hw = full_hw
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(x, weight, bias, y if mod.fuse_relu else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        mod = ctx.mod
+        x, weight, bias, y = ctx.saved_tensors
+        dy = dy.contiguous()
+        st = nv.stream_ptr()
+        if mod.fuse_relu:
+            g = torch.empty_like(dy)
+            nv.call("relu_bwd", nv.ptr(dy), nv.ptr(y), nv.ptr(g), dy.numel(), st)
+            dy = g
+        if ctx.has_bias:
+            gb, acc = grad_buffer(bias)
+            if not acc:
+                gb.zero_()
+            P = dy.shape[0] * dy.shape[1] * dy.shape[2]
+            nv.call("colsum", nv.ptr(dy), nv.ptr(gb), P, mod.Cout, mod.Cout_p, st)
+            _grad_ready(bias)
+        if mod.conv_stride == 2:
+            dy = subsample2_raw(dy, adjoint=True, full_hw=ctx.full_hw)
+        N, H, W, Cin_p = x.shape
+        Ho, Wo = ctx.full_hw
+        # weight gradient
+        gw, acc = grad_buffer(weight)
+        need = nv.lib().dtdl_conv_wgrad_workspace_bytes(N, Ho, Wo, Cin_p, mod.Cout_p, mod.KH, mod.KW)
+        ws = scratch(x.device, need)
+        nv.call("conv_wgrad", nv.ptr(x), nv.ptr(dy), nv.ptr(gw), nv.ptr(ws), ws.numel(), N, H, W,
+                mod.Cin, Cin_p, Ho, Wo, mod.Cout, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad, mod.conv_pad, acc, st)
+        _grad_ready(weight)
+        # data gradient
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = conv_fprop_raw(dy, mod.wd, Cin_p, mod.KH, mod.KW, mod.KH - 1 - mod.conv_pad)
+        return dx, None, None, None
+
+
+def conv(x, mod):
+    return _Conv.apply(x, mod.weight, mod.bias, mod)
+
+
+# --------------------------------------------------------------------------------------
+# batch norm (+ residual) (+ ReLU)
+# --------------------------------------------------------------------------------------
+class _BatchNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, mod, relu):
+        x = x.contiguous()
+        N, H, W, Cp = x.shape
+        P = N * H * W
+        C = mod.num_features
+        st = nv.stream_ptr()
+        stat = mod._stat_buffer(x.device, Cp)
+        y = torch.empty_like(x)
+        training = mod.training or mod.running_mean is None
+        if residual is not None:
+            residual = residual.contiguous()
+        Cres_p = residual.shape[-1] if residual is not None else 0
+        if training:
+            if mod._fwd_dirty:
+                stat[: 2 * Cp].zero_()
+            nv.call("bn_stats", nv.ptr(x), nv.ptr(stat), P, Cp, st)
+            mod._fwd_dirty = True
+        save = torch.empty((2, Cp), dtype=torch.float32, device=x.device)
+        mom = mod.momentum if mod.momentum is not None else 0.1
+        track = mod.track_running_stats and mod.running_mean is not None
+        nv.call("bn_apply", nv.ptr(x), nv.ptr(y), nv.ptr(stat), nv.ptr(gamma), nv.ptr(beta),
+                nv.ptr(mod.running_mean) if track else 0, nv.ptr(mod.running_var) if track else 0,
+                nv.ptr(mod.num_batches_tracked) if (track and training) else 0,
+                nv.ptr(save[0]), nv.ptr(save[1]), nv.ptr(residual), Cres_p, P, C, Cp, mod.eps, mom,
+                1 if relu else 0, 1 if training else 0,
+                stat[2 * Cp:].data_ptr() if training else 0, 2 * Cp, st)
+        ctx.mod, ctx.relu, ctx.Cres_p, ctx.training = mod, relu, Cres_p, training
+        ctx.save_for_backward(x, y if relu else None, gamma, beta, save)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        mod = ctx.mod
+        x, y, gamma, beta, save = ctx.saved_tensors
+        dy = dy.contiguous()
+        N, H, W, Cp = x.shape
+        P = N * H * W
+        st = nv.stream_ptr()
+        stat = mod._stat_buffer(x.device, Cp)
+        if not ctx.training:
+            raise NotImplementedError("backward through eval-mode BatchNorm is not supported")
+        gg, acc_g = grad_buffer(gamma)
+        gb, acc_b = grad_buffer(beta)
+        dx = torch.empty_like(x)
+        dres = None
+        if ctx.Cres_p and ctx.needs_input_grad[3]:
+            dres = torch.empty((N, H, W, ctx.Cres_p), dtype=torch.bfloat16, device=x.device)
+        nv.call("bn_bwd", nv.ptr(dy), nv.ptr(x), nv.ptr(y), nv.ptr(save[0]), nv.ptr(save[1]),
+                nv.ptr(gamma), stat[2 * Cp:].data_ptr(), nv.ptr(dx), nv.ptr(dres), ctx.Cres_p,
+                nv.ptr(gg), nv.ptr(gb), 1 if (acc_g or acc_b) else 0, P, mod.num_features, Cp,
+                1 if ctx.relu else 0, nv.ptr(stat), 2 * Cp, st)
+        mod._fwd_dirty = False
+        _grad_ready(gamma)
+        _grad_ready(beta)
+        return dx, None, None, dres, None, None
+
+
+def batch_norm(x, mod, residual=None, relu=False):
+    return _BatchNorm.apply(x, mod.weight, mod.bias, residual, mod, relu)
+
+
+# --------------------------------------------------------------------------------------
+# pooling
+# --------------------------------------------------------------------------------------
+class _Pool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, stride, pad, mode, ceil_mode):
+        x = x.contiguous()
+        N, H, W, Cp = x.shape
+
+        def osz(n):
+            num = n + 2 * pad - k
+            o = (-(-num // stride) if ceil_mode else num // stride) + 1
+            if ceil_mode and (o - 1) * stride >= n + pad:
+                o -= 1
+            return o
+
+        Ho, Wo = osz(H), osz(W)
+        y = torch.empty((N, Ho, Wo, Cp), dtype=x.dtype, device=x.device)
+        nv.call("pool_fwd", nv.ptr(x), nv.ptr(y), N, H, W, Ho, Wo, Cp, k, stride, pad, mode,
+                nv.stream_ptr())
+        ctx.meta = (k, stride, pad, mode)
+        ctx.save_for_backward(x, y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y = ctx.saved_tensors
+        k, stride, pad, mode = ctx.meta
+        dy = dy.contiguous()
+        N, H, W, Cp = x.shape
+        dx = torch.empty_like(x)
+        nv.call("pool_bwd", nv.ptr(dy), nv.ptr(x), nv.ptr(y), nv.ptr(dx), N, H, W, y.shape[1],
+                y.shape[2], Cp, k, stride, pad, mode, nv.stream_ptr())
+        return dx, None, None, None, None, None
+
+
+def avg_pool(x, k, stride=None, pad=0, ceil_mode=False):
+    return _Pool.apply(x, k, stride or k, pad, 0, ceil_mode)
+
+
+def max_pool(x, k, stride=None, pad=0, ceil_mode=False):
+    return _Pool.apply(x, k, stride or k, pad, 1, ceil_mode)
+
+
+class _GlobalAvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = x.contiguous()
+        N, H, W, Cp = x.shape
+        y = torch.empty((N, 1, 1, Cp), dtype=x.dtype, device=x.device)
+        nv.call("gap_fwd", nv.ptr(x), nv.ptr(y), N, H * W, Cp, nv.stream_ptr())
+        ctx.shape = (N, H, W, Cp)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        N, H, W, Cp = ctx.shape
+        dy = dy.contiguous()
+        dx = torch.empty((N, H, W, Cp), dtype=dy.dtype, device=dy.device)
+        nv.call("gap_bwd", nv.ptr(dy), nv.ptr(dx), N, H * W, Cp, nv.stream_ptr())
+        return dx
+
+
+def global_avg_pool(x):
+    return _GlobalAvgPool.apply(x)
+
+
+class _Flatten(torch.autograd.Function):
+    """NHWC [N,H,W,Cp] -> [N,1,1,pad8(H*W*C)] in NHWC feature order (Keras ``Flatten``)."""
+
+    @staticmethod
+    def forward(ctx, x, C):
+        N, H, W, Cp = x.shape
+        F = H * W * C
+        Fp = pad8(F)
+        ctx.meta = (N, H, W, C, Cp, F, Fp)
+        y = x.new_zeros((N, 1, 1, Fp))
+        y.view(N, Fp)[:, :F] = x[..., :C].reshape(N, F)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        N, H, W, C, Cp, F, Fp = ctx.meta
+        dx = dy.new_zeros((N, H, W, Cp))
+        dx[..., :C] = dy.view(N, Fp)[:, :F].reshape(N, H, W, C)
+        return dx, None
+
+
+def flatten_nhwc(x, C):
+    return _Flatten.apply(x, C)
+
+
+# --------------------------------------------------------------------------------------
+# softmax cross entropy (+ accuracy count), fp32 logits
+# --------------------------------------------------------------------------------------
+class _SoftmaxCE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, targets, stats_out):
+        logits = logits.contiguous().float()
+        N, C = logits.shape
+        out = stats_out if stats_out is not None else torch.zeros(2, device=logits.device)
+        dl = torch.empty_like(logits)
+        nv.call("softmax_ce", nv.ptr(logits), nv.ptr(targets.contiguous()), nv.ptr(out), 0, nv.ptr(dl),
+                N, C, C, 1.0 / N, 1.0 / N, nv.stream_ptr())
+        ctx.save_for_backward(dl)
+        ctx.mark_non_differentiable(out)
+        return out[0].clone(), out
+
+    @staticmethod
+    def backward(ctx, dloss, _):
+        (dl,) = ctx.saved_tensors
+        return dl * dloss, None, None
+
+
+def softmax_cross_entropy(logits, targets, stats_out=None):
+    """Mean cross entropy; also returns a 2-vector [loss, #correct] accumulated on device."""
+    return _SoftmaxCE.apply(logits, targets, stats_out)

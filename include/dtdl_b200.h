@@ -1,0 +1,127 @@
+/* C ABI of libdtdl_b200.so -- the sm_100a kernels and peer-memory runtime of the
+ * B200-native data-parallel training framework.
+ *
+ * Conventions
+ *   - Every function returns 0 on success; on failure it returns non-zero and
+ *     dtdl_last_error() describes why (thread local).
+ *   - Activations are NHWC bf16 with the channel count padded to a multiple of
+ *     8 ("Cp"); pad channels hold zeros.  `P` is the number of pixels N*H*W.
+ *   - `stream` is a cudaStream_t passed as void* (0 = default stream).  All work
+ *     is asynchronous on that stream; nothing here synchronises the device.
+ *   - Functions are safe to capture in a CUDA graph unless stated otherwise.
+ *
+ * Each block names the reference behaviour it provides (paths are relative to
+ * MyXiaoPao/distributed-training-dl).
+ */
+#ifndef DTDL_B200_H_
+#define DTDL_B200_H_
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* dtdl_last_error(void);
+int dtdl_version(void);
+
+/* ---- tensor-core ops (tcgen05 + TMEM + TMA) ------------------------------------------
+ * Stride-1 convolution / linear forward as implicit GEMM (nn.Conv2d / nn.Linear in
+ * pytorch/model.py:28-32,62-63,77; Keras Conv2D/Dense in tensorflow2/mnist_single.py:17-26;
+ * Chainer L.Linear in chainer/train_mnist.py:19-21).  `wpack` comes from dtdl_pack_weights.
+ * The data gradient is the same call on dy with the dgrad pack and pad' = K-1-pad.
+ * flags: 1 = ReLU epilogue, 2 = fp32 output (default bf16). */
+int dtdl_conv_fprop(const void* x, const void* wpack, void* y, const float* bias, int N, int H,
+                    int W, int Cin_p, int Ho, int Wo, int Cout_p, int KH, int KW, int pad_h,
+                    int pad_w, int flags, void* stream);
+
+/* Weight gradient (autograd of the layers above; pytorch/single_gpu.py:102).  Writes (or
+ * accumulates into) the fp32 OIHW gradient `dw`.  Needs scratch of the size returned by
+ * dtdl_conv_wgrad_workspace_bytes for the same shape. */
+long long dtdl_conv_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cin_p, int Cout_p, int KH,
+                                          int KW);
+int dtdl_conv_wgrad(const void* x, const void* dy, float* dw, void* workspace,
+                    long long workspace_bytes, int N, int H, int W, int Cin, int Cin_p, int Ho,
+                    int Wo, int Cout, int Cout_p, int KH, int KW, int pad_h, int pad_w,
+                    int accumulate, void* stream);
+
+/* fp32 master weights -> bf16 operand packs for a whole model in one launch. */
+int dtdl_pack_entry_size(void);
+long long dtdl_pack_entry_fill(void* entry, const float* w, void* wf, void* wd, int Cout, int Cin,
+                               int taps, int Cin_p, int Cout_p, long long first_block);
+int dtdl_pack_weights(const void* device_table, int n_entries, long long total_blocks,
+                      void* stream);
+
+/* ---- bandwidth-bound layer ops --------------------------------------------------------
+ * BatchNorm2d train/eval (pytorch/model.py:27,30,33,64,74), ReLU (:34,75), residual add with
+ * zero-padded shortcut (:18,49), pooling (:11,76; tensorflow2/mnist_single.py:19,21),
+ * softmax cross entropy + accuracy count (pytorch/single_gpu.py:99,105-108). */
+int dtdl_nchw_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, int Cp,
+                           void* stream);
+int dtdl_bn_stats(const void* x, float* sums /* [2*Cp], zeroed */, long long P, int Cp,
+                  void* stream);
+int dtdl_bn_apply(const void* x, void* y, const float* sums, const float* gamma, const float* beta,
+                  float* running_mean, float* running_var, long long* num_batches_tracked,
+                  float* save_mean, float* save_rstd, const void* residual, int Cres_p, long long P,
+                  int C, int Cp, float eps, float momentum, int relu, int training, float* zero_buf,
+                  int zero_n, void* stream);
+int dtdl_bn_bwd(const void* dy, const void* x, const void* y, const float* save_mean,
+                const float* save_rstd, const float* gamma, float* sums2 /* [2*Cp], zeroed */,
+                void* dx, void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
+                long long P, int C, int Cp, int relu, float* zero_buf, int zero_n, void* stream);
+int dtdl_relu_bwd(const void* dy, const void* y, void* dx, long long n_elems, void* stream);
+int dtdl_add_bf16(const void* a, const void* b, void* out, long long n_elems, void* stream);
+int dtdl_add_prefix_bf16(void* a, const void* b, long long P, int Ca_p, int Cb_p, void* stream);
+int dtdl_pool_fwd(const void* x, void* y, int N, int H, int W, int Ho, int Wo, int Cp, int k,
+                  int stride, int pad, int mode /* 0 avg, 1 max */, void* stream);
+int dtdl_pool_bwd(const void* dy, const void* x, const void* y, void* dx, int N, int H, int W,
+                  int Ho, int Wo, int Cp, int k, int stride, int pad, int mode, void* stream);
+int dtdl_subsample2(const void* x, void* y, int N, int H, int W, int Cp, int adjoint,
+                    void* stream);
+int dtdl_gap_fwd(const void* x, void* y, int N, int HW, int Cp, void* stream);
+int dtdl_gap_bwd(const void* dy, void* dx, int N, int HW, int Cp, void* stream);
+int dtdl_softmax_ce(const float* logits, const long long* targets, float* out2 /* loss, correct */,
+                    void* dlogits_bf16, float* dlogits_f32, int N, int C, int Cp, float inv_n,
+                    float grad_scale, void* stream);
+int dtdl_colsum(const void* x, float* out /* zeroed */, long long P, int C, int Cp, void* stream);
+int dtdl_f32_to_bf16_pad(const float* x, void* y, long long rows, int cols, int cols_p,
+                         void* stream);
+int dtdl_bf16_to_f32_unpad(const void* x, float* y, long long rows, int cols, int cols_p,
+                           void* stream);
+
+/* ---- peer-memory runtime and collectives ----------------------------------------------
+ * Replaces the NCCL calls made by DistributedDataParallel / nn.DataParallel / ChainerMN /
+ * MirroredStrategy (pytorch/distributed_data_parallel.py:61-62,74,132; pytorch/data_parallel.py:71;
+ * chainer/train_mnist_multi.py:55,81-82; tensorflow2/mnist_mirror_strategy.py:12).
+ * "Symmetric" buffers have the same size on every rank; `bufs[r]` is rank r's base pointer as
+ * seen from the calling process (cudaIpcOpenMemHandle across processes, peer access inside
+ * one).  All ranks must issue the same sequence of collective calls. */
+int dtdl_comm_create(int rank, int world, void** handle, void** flags_ptr);
+int dtdl_comm_set_peer_flags(void* handle, int peer, void* flags_ptr);
+int dtdl_comm_destroy(void* handle);
+int dtdl_symm_alloc(long long bytes, void** ptr);
+int dtdl_symm_free(void* ptr);
+int dtdl_ipc_get_handle(void* ptr, void* out64);
+int dtdl_ipc_open_handle(const void* in64, void** ptr);
+int dtdl_ipc_close_handle(void* ptr);
+int dtdl_enable_peer_access(int dev, int peer);
+int dtdl_comm_barrier(void* handle, void* stream);
+int dtdl_comm_allreduce(void* handle, void* const* grads, void* const* dst, long long offset_bytes,
+                        long long n, float scale, int two_shot, int max_blocks, void* stream);
+/* opt: 1 = SGD momentum, 2 = Adam (torch), 3 = Adam (Keras epsilon placement).
+ * hyper: device float[16] = lr, momentum, weight_decay, 1/world, beta1, beta2, eps,
+ *        1-beta1^t, sqrt(1-beta2^t), dampening. */
+int dtdl_comm_reduce_update(void* handle, void* const* grads, void* const* params, float* mom,
+                            float* var, const float* hyper, long long offset_bytes, long long n,
+                            int opt, int two_shot, int max_blocks, void* stream);
+int dtdl_comm_broadcast(void* handle, void* const* bufs, long long offset_bytes, long long bytes,
+                        int root, int max_blocks, void* stream);
+int dtdl_comm_allgather(void* handle, void* const* bufs, long long offset_bytes, long long bytes,
+                        int max_blocks, void* stream);
+/* Single-rank optimizer step (torch.optim.SGD / Adam: pytorch/single_gpu.py:71-72,103;
+ * chainer/train_mnist.py:69). */
+int dtdl_local_update(float* param, const float* grad, float* mom, float* var, const float* hyper,
+                      long long n, int opt, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DTDL_B200_H_ */

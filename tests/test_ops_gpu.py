@@ -1,0 +1,190 @@
+"""Kernel-vs-oracle numerics on the GPU: every sm_100a op against plain PyTorch fp32.
+
+Inputs and weights are rounded to bf16 first so the oracle sees the same operands; the
+remaining difference is fp32 accumulation order plus one bf16 rounding of the output.
+"""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf(x):
+    return x.to(torch.bfloat16).to(torch.float32)
+
+
+def _nhwc_to_nchw(y, C):
+    return y[..., :C].permute(0, 3, 1, 2).float()
+
+
+def _rel_err(a, b):
+    return ((a - b).abs().max() / (b.abs().max() + 1e-6)).item()
+
+
+CONV_CASES = [
+    # N, Cin, Cout, H, W, k, pad, stride
+    (4, 3, 16, 32, 32, 3, 1, 1),
+    (4, 21, 26, 32, 32, 3, 1, 1),
+    (2, 64, 64, 32, 32, 3, 1, 1),
+    (4, 101, 106, 32, 32, 3, 1, 2),
+    (4, 146, 151, 16, 16, 3, 1, 1),
+    (8, 266, 271, 8, 8, 3, 1, 1),
+    (4, 1, 32, 28, 28, 3, 0, 1),
+    (4, 32, 64, 13, 13, 3, 0, 1),
+    (4, 64, 64, 5, 5, 3, 0, 1),
+    (2, 64, 256, 14, 14, 1, 0, 1),
+    (3, 300, 520, 7, 7, 1, 0, 1),
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_forward_backward(case):
+    from distributed_training_dl_b200.ops import Conv2d, functional as fn
+    N, Cin, Cout, H, W, k, pad, stride = case
+    torch.manual_seed(0)
+    conv = Conv2d(Cin, Cout, k, stride=stride, padding=pad, bias=False).cuda()
+    with torch.no_grad():
+        conv.weight.copy_(_bf(conv.weight))
+    x = _bf(torch.randn(N, Cin, H, W, device="cuda"))
+    xn = fn.to_nhwc(x).requires_grad_(True)
+    y = conv(xn)
+    ref_x = x.clone().requires_grad_(True)
+    ref_w = conv.weight.detach().clone().requires_grad_(True)
+    ref_y = F.conv2d(ref_x, ref_w, stride=stride, padding=pad)
+    assert y.shape[1:3] == ref_y.shape[2:]
+    assert _rel_err(_nhwc_to_nchw(y, Cout), ref_y) < 1e-2
+    assert y[..., Cout:].abs().max().item() == 0 if y.shape[-1] > Cout else True
+
+    dy = _bf(torch.randn_like(ref_y))
+    ref_y.backward(dy)
+    y.backward(fn.to_nhwc(dy))
+    assert _rel_err(_nhwc_to_nchw(xn.grad, Cin), ref_x.grad) < 1e-2
+    assert _rel_err(conv.weight.grad, ref_w.grad) < 1e-2
+
+
+@pytest.mark.parametrize("N,Fin,Fout", [(64, 784, 1000), (100, 1000, 10), (7, 271, 10), (256, 576, 64)])
+def test_linear_forward_backward(N, Fin, Fout):
+    from distributed_training_dl_b200.ops import Linear, functional as fn
+    torch.manual_seed(0)
+    lin = Linear(Fin, Fout, activation="relu").cuda()
+    with torch.no_grad():
+        lin.weight.copy_(_bf(lin.weight))
+    x = _bf(torch.randn(N, Fin, device="cuda"))
+    xn = fn.to_nhwc(x).requires_grad_(True)
+    y = lin(xn)
+    rx = x.clone().requires_grad_(True)
+    rw = lin.weight.detach().clone().requires_grad_(True)
+    rb = lin.bias.detach().clone().requires_grad_(True)
+    ry = F.relu(F.linear(rx, rw, rb))
+    assert _rel_err(y.view(N, -1)[:, :Fout].float(), ry) < 1e-2
+    dy = _bf(torch.randn_like(ry))
+    ry.backward(dy)
+    y.backward(fn.to_nhwc(dy))
+    assert _rel_err(xn.grad.view(N, -1)[:, :Fin].float(), rx.grad) < 1e-2
+    assert _rel_err(lin.weight.grad, rw.grad) < 1e-2
+    assert _rel_err(lin.bias.grad, rb.grad) < 1e-2
+
+
+@pytest.mark.parametrize("C,Cres,relu,HW,N", [(21, 16, False, 32, 8), (26, 0, True, 16, 8), (271, 271, True, 8, 16),
+                                            (64, 64, True, 7, 4)])
+def test_batchnorm_forward_backward(C, Cres, relu, HW, N):
+    from distributed_training_dl_b200.ops import BatchNorm2d, functional as fn
+    torch.manual_seed(0)
+    bn = BatchNorm2d(C).cuda()
+    ref = torch.nn.BatchNorm2d(C).cuda()
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5)
+        bn.bias.uniform_(-0.5, 0.5)
+        ref.weight.copy_(bn.weight)
+        ref.bias.copy_(bn.bias)
+    x = _bf(torch.randn(N, C, HW, HW, device="cuda") * 2 + 0.5)
+    res = _bf(torch.randn(N, Cres, HW, HW, device="cuda")) if Cres else None
+    xn = fn.to_nhwc(x).requires_grad_(True)
+    rn = fn.to_nhwc(res).requires_grad_(True) if Cres else None
+    y = bn(xn, residual=rn, relu=relu)
+    rx = x.clone().requires_grad_(True)
+    rr = res.clone().requires_grad_(True) if Cres else None
+    ry = ref(rx)
+    if Cres:
+        ry = ry + F.pad(rr, (0, 0, 0, 0, 0, C - Cres))
+    if relu:
+        ry = F.relu(ry)
+    assert _rel_err(_nhwc_to_nchw(y, C), ry) < 2e-2
+    assert torch.allclose(bn.running_mean, ref.running_mean, atol=1e-3)
+    assert torch.allclose(bn.running_var, ref.running_var, rtol=1e-2, atol=1e-3)
+    assert int(bn.num_batches_tracked) == 1
+    dy = _bf(torch.randn_like(ry))
+    ry.backward(dy)
+    y.backward(fn.to_nhwc(dy))
+    assert _rel_err(_nhwc_to_nchw(xn.grad, C), rx.grad) < 3e-2
+    assert _rel_err(bn.weight.grad, ref.weight.grad) < 2e-2
+    assert _rel_err(bn.bias.grad, ref.bias.grad) < 2e-2
+    if Cres:
+        assert _rel_err(_nhwc_to_nchw(rn.grad, Cres), rr.grad) < 1e-2
+    # second step exercises the folded re-zeroing of the statistics scratch
+    y2 = bn(xn, residual=rn, relu=relu)
+    ry2 = ref(rx)
+    if Cres:
+        ry2 = ry2 + F.pad(rr, (0, 0, 0, 0, 0, C - Cres))
+    if relu:
+        ry2 = F.relu(ry2)
+    assert _rel_err(_nhwc_to_nchw(y2, C), ry2) < 2e-2
+
+
+@pytest.mark.parametrize("mode,k,s,p,H", [("avg", 2, 2, 0, 32), ("max", 2, 2, 0, 26), ("max", 3, 2, 1, 16), ("avg", 8, 1, 0, 8)])
+def test_pooling(mode, k, s, p, H):
+    from distributed_training_dl_b200.ops import AvgPool2d, MaxPool2d, functional as fn
+    torch.manual_seed(0)
+    C, N = 21, 4
+    x = _bf(torch.randn(N, C, H, H, device="cuda"))
+    xn = fn.to_nhwc(x).requires_grad_(True)
+    mod = (AvgPool2d if mode == "avg" else MaxPool2d)(k, stride=s, padding=p)
+    y = mod(xn)
+    rx = x.clone().requires_grad_(True)
+    ry = (F.avg_pool2d if mode == "avg" else F.max_pool2d)(rx, k, s, p)
+    assert _rel_err(_nhwc_to_nchw(y, C), ry) < 1e-2
+    dy = _bf(torch.randn_like(ry))
+    ry.backward(dy)
+    y.backward(fn.to_nhwc(dy).view_as(y))
+    assert _rel_err(_nhwc_to_nchw(xn.grad, C), rx.grad) < 1e-2
+
+
+def test_softmax_cross_entropy():
+    from distributed_training_dl_b200.ops import functional as fn
+    torch.manual_seed(0)
+    logits = torch.randn(64, 10, device="cuda", requires_grad=True)
+    t = torch.randint(0, 10, (64,), device="cuda")
+    loss, stats = fn.softmax_cross_entropy(logits, t)
+    ref_l = logits.detach().clone().requires_grad_(True)
+    ref = F.cross_entropy(ref_l, t)
+    assert abs(loss.item() - ref.item()) < 1e-4
+    assert int(stats[1].item()) == int((ref_l.argmax(1) == t).sum().item())
+    loss.backward()
+    ref.backward()
+    assert torch.allclose(logits.grad, ref_l.grad, atol=1e-5)
+
+
+def test_models_match_cpu_oracle():
+    """Whole-model forward/backward on the GPU kernels vs the same module on CPU fp32."""
+    import copy
+    from distributed_training_dl_b200.models import MLP, MnistCNN, pyramidnet
+    torch.manual_seed(0)
+    for make, shape, tol in [(lambda: MLP(128), (32, 784), 3e-2), (MnistCNN, (16, 1, 28, 28), 3e-2),
+                             (pyramidnet, (8, 3, 32, 32), 0.15)]:
+        cpu = make()
+        gpu = copy.deepcopy(cpu).cuda()
+        x = torch.randn(*shape)
+        t = torch.randint(0, 10, (shape[0],))
+        lc = F.cross_entropy(cpu(x), t)
+        lg = F.cross_entropy(gpu(x.cuda()), t.cuda())
+        assert abs(lc.item() - lg.item()) < tol * max(1.0, abs(lc.item())), (lc.item(), lg.item())
+        lc.backward()
+        lg.backward()
+        name, pc = next(iter(cpu.named_parameters()))
+        worst = 0.0
+        for (n, a), (_, b) in zip(cpu.named_parameters(), gpu.named_parameters()):
+            assert b.grad is not None, n
+            e = _rel_err(b.grad.cpu(), a.grad)
+            worst = max(worst, e)
+        assert worst < (1.0 if make is pyramidnet else 0.1), worst
