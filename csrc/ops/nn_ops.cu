@@ -444,10 +444,28 @@ __global__ void pool_bwd_kernel(const uint4* __restrict__ dy, const uint4* __res
         const long long oi = ((n * Ho + ho) * Wo + wo) * G + g;
         const F8 d = unpack8(dy[oi]);
         if (mode) {
+          // torch routes the gradient to the FIRST maximum of the window (row-major scan);
+          // bf16 data ties often, so check that no earlier tap holds the same value.
           const F8 yv = unpack8(y[oi]);
+          bool mine[8];
+#pragma unroll
+          for (int q = 0; q < 8; ++q) mine[q] = xv.v[q] == yv.v[q];
+          for (int rr = 0; rr <= r; ++rr) {
+            const int hh = ho * stride - pad + rr;
+            if (hh < 0 || hh >= H) continue;
+            const int s_end = rr < r ? k : s;
+            for (int sc = 0; sc < s_end; ++sc) {
+              const int ww = wo * stride - pad + sc;
+              if (ww < 0 || ww >= W) continue;
+              const F8 ev = unpack8(x[((n * H + hh) * W + ww) * G + g]);
+#pragma unroll
+              for (int q = 0; q < 8; ++q)
+                if (ev.v[q] == yv.v[q]) mine[q] = false;
+            }
+          }
 #pragma unroll
           for (int q = 0; q < 8; ++q)
-            if (xv.v[q] == yv.v[q]) acc.v[q] += d.v[q];
+            if (mine[q]) acc.v[q] += d.v[q];
         } else {
           int hs = ho * stride - pad, ws = wo * stride - pad;
           int he = hs + k < H ? hs + k : H, we = ws + k < W ? ws + k : W;

@@ -41,6 +41,7 @@ def grad_buffer(p: torch.Tensor):
     if p.grad is not g:
         p.grad = g
     p._dtdl_fresh = False
+    p._dtdl_native = True
     return g, (0 if fresh else 1)
 
 

@@ -1,0 +1,230 @@
+"""``wrap(model)``: the drop-in data-parallel wrapper (one process per GPU).
+
+Same contract as ``torch.nn.parallel.DistributedDataParallel`` as the reference uses it
+(pytorch/distributed_data_parallel.py:74,128-133): the wrapped model is called like the bare
+one, ``.module`` is the original, ``state_dict()`` keys carry the ``module.`` prefix
+(pytorch/data_parallel.py:87-90) while ``.module.state_dict()`` is bare (:108-114), parameters
+and buffers are broadcast from rank 0 at construction, buffers (BatchNorm running statistics)
+are re-broadcast at every forward, and gradients are averaged over ranks during backward,
+bucket by bucket, overlapped with the rest of backward on a side stream.
+
+What is different underneath (``backend="b200"``): parameters, gradients and buffers live in
+symmetric peer-memory arenas; a bucket's all-reduce is a hand-written kernel reading /
+writing peer memory over NVLink, and when a fused optimizer is attached the same kernel applies
+1/W, weight decay and the SGD/Adam update and scatters updated parameters -- so there is no
+separate ``optimizer.step()`` pass.  ``backend="gloo"`` (CPU) and ``"nccl"`` run the same
+bucket logic over ``torch.distributed`` collectives.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from ..ops import functional as fn
+from ..ops.modules import packed_layers
+from . import rendezvous
+from .arena import BufferArena, ParamArena
+
+
+class Reducer:
+    """Bucketed gradient reducer.  Buckets launch strictly in index order on every rank, so
+    all ranks issue the same sequence of collectives whatever the local gradient order."""
+
+    def __init__(self, module, comm, bucket_cap_mb=25.0, first_bucket_mb=1.0, broadcast_buffers=True):
+        self.module, self.comm = module, comm
+        self.world, self.rank = comm.size, comm.rank
+        self.device = next(module.parameters()).device
+        self.backend = comm.backend if self.world > 1 else ("b200" if self.device.type == "cuda" else "gloo")
+        self.peer = comm.peer if (comm.backend == "b200" and self.device.type == "cuda") else None
+        self.arena = ParamArena(module.parameters(), self.device, peer=self.peer,
+                                bucket_cap_mb=bucket_cap_mb, first_bucket_mb=first_bucket_mb)
+        self.arena.reducer = self
+        self.buffers = BufferArena(list(module.buffers()), self.device, peer=self.peer)
+        self.broadcast_buffers = broadcast_buffers
+        self.packed_modules = packed_layers(module) if self.device.type == "cuda" else []
+        self.optimizer = None
+        self.state_sharded = False
+        self.require_sync = True
+        self.comm_stream = torch.cuda.Stream(self.device) if self.device.type == "cuda" else None
+        self._pending = None
+        self._next = 0
+        self._works = []
+        self._launched_any = False
+        self._callback_queued = False
+        self._hook = fn.add_ready_hook(self._on_ready)
+        for p in self.arena.params:
+            p.register_post_accumulate_grad_hook(self._torch_hook)
+        self.sync_parameters()
+
+    # ------------------------------------------------------------------ construction-time sync
+    def sync_parameters(self):
+        """Rank 0's parameters and buffers become everyone's (K-C1)."""
+        if self.world == 1:
+            return
+        if self.peer is not None:
+            torch.cuda.synchronize(self.device)
+            self.peer.broadcast(self.arena.param_buf, 0, self.arena.numel * 4, root=0)
+            self.peer.broadcast(self.buffers.buf, 0, self.buffers.nbytes, root=0)
+            torch.cuda.synchronize(self.device)
+        else:
+            dist.broadcast(self.arena.param_flat, src=0, group=self.comm.group)
+            dist.broadcast(self.buffers.bytes, src=0, group=self.comm.group)
+        for m in self.packed_modules:
+            m._packed_version = None
+
+    def sync_buffers(self):
+        """Per-forward BatchNorm running-stat sync from rank 0 (K-C2)."""
+        if self.world == 1 or not self.broadcast_buffers or self.buffers.nbytes <= 16:
+            return
+        if self.peer is not None:
+            self.peer.broadcast(self.buffers.buf, 0, self.buffers.nbytes, root=0, max_blocks=4)
+        else:
+            dist.broadcast(self.buffers.bytes, src=0, group=self.comm.group)
+
+    # ------------------------------------------------------------------ backward-time reduction
+    def prepare(self):
+        """Start of an iteration: every bucket waits for all of its gradients."""
+        if self._pending is not None and self._next not in (0, len(self.arena.buckets)):
+            self.flush()
+        self._pending = [len(b.params) for b in self.arena.buckets]
+        self._next = 0
+        self._launched_any = False
+        if self.optimizer is not None:
+            self.optimizer.refresh_hyper()
+
+    def _torch_hook(self, p):
+        # gradients produced by stock torch ops land in p.grad; move them into the arena
+        # (autograd accumulates into p.grad itself, so p.grad always holds the full value)
+        g = p._dtdl_grad
+        if p.grad is not None and p.grad.data_ptr() != g.data_ptr():
+            g.copy_(p.grad)
+            p.grad = g
+        p._dtdl_fresh = False
+        self._on_ready(p)
+
+    def _on_ready(self, p):
+        if self._pending is None or getattr(p, "_dtdl_arena", None) is not self.arena:
+            return
+        if not self._callback_queued:
+            # end-of-backward: launch leftovers; without a fused optimizer also join, so that
+            # p.grad holds the averaged gradient when backward() returns (DDP's contract)
+            self._callback_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(self._backward_done)
+        b = self.arena.bucket_of[id(p)]
+        self._pending[b] -= 1
+        while self._next < len(self.arena.buckets) and self._pending[self._next] <= 0:
+            self._launch(self.arena.buckets[self._next])
+            self._next += 1
+
+    def _backward_done(self):
+        self._callback_queued = False
+        if not self.require_sync:
+            return
+        if self.optimizer is None:
+            self.finish_step(fused=False)
+        else:
+            self.flush()
+
+    def _fused(self):
+        return self.optimizer is not None and self.require_sync
+
+    def _launch(self, bucket):
+        if not self.require_sync:
+            return
+        off_b, n = bucket.offset * 4, bucket.numel
+        a = self.arena
+        if self.peer is not None and self.world > 1:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.device))
+            self.comm_stream.wait_event(ev)
+            if self._fused():
+                opt = self.optimizer
+                m = opt._state_flat[opt.state_names[0]]
+                v = opt._state_flat[opt.state_names[1]] if len(opt.state_names) > 1 else None
+                two = self.peer.choose_two_shot(n * 4)
+                self.state_sharded = self.state_sharded or bool(two)
+                self.peer.reduce_update(a.grad_buf, a.param_buf, m, v, opt._hyper_dev, off_b, n,
+                                        opt.opt_code, two_shot=two, stream=self.comm_stream)
+            else:
+                self.peer.allreduce(a.grad_buf, off_b, n, scale=1.0 / self.world, stream=self.comm_stream)
+        elif self.world > 1:
+            g = a.grad_flat[bucket.offset: bucket.offset + n]
+            work = dist.all_reduce(g, group=self.comm.group, async_op=True)
+            self._works.append((work, bucket))
+        self._launched_any = True
+
+    def flush(self):
+        """Launches whatever has not been launched (parameters that received no gradient)."""
+        if self._pending is None:
+            return
+        while self._next < len(self.arena.buckets):
+            self._launch(self.arena.buckets[self._next])
+            self._next += 1
+
+    def finish_step(self, fused):
+        """Called by ``optimizer.step()`` (fused) or by the wrapper before a torch optimizer."""
+        self.flush()
+        a = self.arena
+        if self.peer is not None and self.world > 1:
+            torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+        elif self.world > 1:
+            for work, bucket in self._works:
+                work.wait()
+                g = a.grad_flat[bucket.offset: bucket.offset + bucket.numel]
+                g.div_(self.world)
+                if fused:
+                    self.optimizer._update_torch(a.grad_flat, bucket.offset, bucket.numel)
+            self._works = []
+        if fused and self.world == 1:
+            self.optimizer._local_update()
+        self._pending = None
+
+    def wait(self):
+        """Makes reduced gradients visible to the current stream (non-fused use)."""
+        self.finish_step(fused=False)
+
+
+class DistributedModel(nn.Module):
+    def __init__(self, module, comm=None, optimizer=None, bucket_cap_mb=25.0, first_bucket_mb=1.0,
+                 broadcast_buffers=True, device_ids=None, output_device=None):
+        super().__init__()
+        comm = comm or rendezvous.current() or rendezvous.init()
+        self.module = module
+        self.comm = comm
+        self.reducer = Reducer(module, comm, bucket_cap_mb, first_bucket_mb, broadcast_buffers)
+        if optimizer is not None:
+            optimizer.attach(self.reducer)
+
+    def forward(self, *args, **kwargs):
+        red = self.reducer
+        if self.training and torch.is_grad_enabled():
+            red.sync_buffers()
+            red.prepare()
+        return self.module(*args, **kwargs)
+
+    # gradient accumulation: skip the collective, let gradients add up locally
+    def no_sync(self):
+        model = self
+
+        class _NoSync:
+            def __enter__(self_inner):
+                model.reducer.require_sync = False
+
+            def __exit__(self_inner, *exc):
+                model.reducer.require_sync = True
+
+        return _NoSync()
+
+    def wait_gradients(self):
+        """For stock torch optimizers: call before ``optimizer.step()`` (a fused optimizer does it)."""
+        self.reducer.wait()
+
+
+def wrap(model, optimizer=None, comm=None, **kw) -> DistributedModel:
+    """``net = wrap(net)`` replaces ``DistributedDataParallel(net, device_ids=[gpu])``."""
+    return DistributedModel(model, comm=comm, optimizer=optimizer, **kw)
+
+
+# torch spelling kept for drop-in use
+DistributedDataParallel = DistributedModel

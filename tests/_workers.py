@@ -1,0 +1,114 @@
+"""Worker bodies for the multi-process (gloo) tests; must be importable for mp spawn."""
+import copy
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def _gather(comm, t):
+    return comm.allgather_object(t.detach().cpu())
+
+
+def ddp_equivalence(i, world, init_kind, port, outdir):
+    import distributed_training_dl_b200 as dtdl
+    from distributed_training_dl_b200.models import MLP
+    torch.set_num_threads(2)
+    if init_kind == "tcp":
+        comm = dtdl.init(backend="gloo", init_method=f"tcp://127.0.0.1:{port}", rank=i, world_size=world)
+    else:  # env:// variables were exported by dtdl.spawn
+        comm = dtdl.init(backend="gloo")
+    assert comm.rank == i and comm.size == world
+    torch.manual_seed(100 + i)           # different init on every rank on purpose
+    net = dtdl.wrap(MLP(n_units=24))
+    # (a) identical parameters after construction == rank 0's
+    for p in net.parameters():
+        allp = _gather(comm, p)
+        assert all(torch.equal(allp[0], q) for q in allp)
+    # (d) state_dict spellings
+    bare_keys = list(MLP(n_units=24).state_dict().keys())
+    assert list(net.module.state_dict().keys()) == bare_keys
+    assert list(net.state_dict().keys()) == ["module." + k for k in bare_keys]
+
+    ref = copy.deepcopy(net.module)      # single-process model fed the concatenated batch
+    for p in ref.parameters():
+        p.grad = None
+    opt = dtdl.FusedSGD(net.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+    ropt = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+    g = torch.Generator().manual_seed(7)
+    for step in range(3):
+        xs = torch.randn(world, 8, 784, generator=g)
+        ts = torch.randint(0, 10, (world, 8), generator=g)
+        out = net(xs[i])
+        loss = F.cross_entropy(out, ts[i])
+        opt.zero_grad()
+        loss.backward()
+        if step == 0:
+            # (b) the reduced gradient is the mean of the per-rank local gradients
+            local = copy.deepcopy(ref)
+            F.cross_entropy(local(xs[i]), ts[i]).backward()
+            net.reducer.flush()
+            for work, bucket in net.reducer._works:
+                work.wait()
+            for (n_, p), q in zip(net.module.named_parameters(), local.parameters()):
+                mean = sum(_gather(comm, q.grad)) / world
+                got = p._dtdl_grad / world   # all_reduce summed; division happens in finish_step
+                assert torch.allclose(got, mean, atol=1e-5), n_
+        opt.step()
+        rl = F.cross_entropy(ref(xs.reshape(-1, 784)), ts.reshape(-1))
+        ropt.zero_grad()
+        rl.backward()
+        ropt.step()
+        # (c) k steps == single process on the concatenated batch
+        for p, q in zip(net.module.parameters(), ref.parameters()):
+            assert torch.allclose(p, q, atol=2e-5)
+    for p in net.parameters():
+        allp = _gather(comm, p)
+        assert all(torch.equal(allp[0], q) for q in allp)
+    # optimizer state in torch format
+    sd = opt.state_dict()
+    assert "momentum_buffer" in sd["state"][0]
+    dtdl.save_model(net.module, os.path.join(outdir, "ddp.pth"), per_rank=True)
+    comm.barrier()
+    assert os.path.exists(os.path.join(outdir, f"ddp_{i}.pth"))
+    open(os.path.join(outdir, f"ok_{i}"), "w").write("ok")
+    dtdl.shutdown()
+
+
+def ddp_pyramidnet(i, world, port, outdir):
+    """BASELINE.json config 1: the reference CNN under the DDP-style wrapper on CPU/gloo."""
+    import distributed_training_dl_b200 as dtdl
+    from distributed_training_dl_b200.models import pyramidnet
+    torch.set_num_threads(4)
+    comm = dtdl.init(backend="gloo", init_method=f"tcp://127.0.0.1:{port}", rank=i, world_size=world)
+    torch.manual_seed(i)
+    net = dtdl.wrap(pyramidnet())
+    opt = dtdl.FusedSGD(net.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    sched = torch.optim.lr_scheduler.StepLR(opt, step_size=2, gamma=0.1)
+    ds = dtdl.SyntheticDataset("cifar", length=8, seed=1)
+    sampler = dtdl.DistributedSampler(ds)
+    loader = torch.utils.data.DataLoader(ds, batch_size=2, sampler=sampler)
+    net.train()
+    losses = []
+    for x, t in loader:
+        loss = F.cross_entropy(net(x), t)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    sched.step()
+    assert all(l == l for l in losses)
+    # replicas stay bit-identical; BN running stats follow rank 0 (broadcast at every forward)
+    chk = torch.cat([p.detach().flatten()[:64] for p in net.parameters()])
+    allc = comm.allgather_object(chk)
+    assert all(torch.equal(allc[0], c) for c in allc)
+    net(torch.randn(2, 3, 32, 32))
+    rm = comm.allgather_object(net.module.bn1.running_mean.clone())
+    open(os.path.join(outdir, f"ok_{i}"), "w").write("ok")
+    dtdl.shutdown()

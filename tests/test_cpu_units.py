@@ -1,0 +1,205 @@
+"""CPU unit tests: rendezvous spec parsing, sampler, checkpoints, fused optimizers, models."""
+import copy
+import os
+
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+import distributed_training_dl_b200 as dtdl
+from distributed_training_dl_b200 import parallel as par
+from distributed_training_dl_b200.models import MLP, MnistCNN, pyramidnet, pyramid_widths
+
+
+def test_slurm_nodelist():
+    assert par.expand_slurm_nodelist("gpu[01-03,07],login1") == ["gpu01", "gpu02", "gpu03", "gpu07", "login1"]
+    assert par.expand_slurm_nodelist("c1") == ["c1"]
+    assert par.expand_slurm_nodelist("n[9-11]") == ["n9", "n10", "n11"]
+
+
+def test_rendezvous_specs():
+    s = par.resolve_spec("tcp://c1:20201", rank=3, world_size=4, env={})
+    assert (s.master_addr, s.master_port, s.rank, s.world_size) == ("c1", 20201, 3, 4)
+    with pytest.raises(ValueError):
+        par.resolve_spec("tcp://c1:20201", env={})
+    env = {"RANK": "5", "WORLD_SIZE": "8", "MASTER_ADDR": "10.0.0.1", "MASTER_PORT": "1234", "LOCAL_RANK": "1"}
+    s = par.resolve_spec("env://", env=env)
+    assert (s.rank, s.world_size, s.local_rank, s.init_method) == (5, 8, 1, "tcp://10.0.0.1:1234")
+    assert par.resolve_spec(None, env=env).source == "env"
+    senv = {"SLURM_PROCID": "9", "SLURM_NTASKS": "16", "SLURM_LOCALID": "1", "SLURM_JOB_NODELIST": "gpu[3-4]",
+            "SLURM_JOB_ID": "77"}
+    s = par.resolve_spec(None, env=senv)
+    assert (s.source, s.rank, s.world_size, s.local_rank, s.master_addr) == ("slurm", 9, 16, 1, "gpu3")
+    s = par.resolve_spec(worker_hosts="a:2222,a:2223,b:2222", task_index=2, env={})
+    assert (s.rank, s.world_size, s.master_addr, s.master_port, s.local_rank) == (2, 3, "a", 2222, 0)
+    assert par.resolve_spec(None, env={}).world_size == 1
+
+
+def test_sampler_matches_torch():
+    from torch.utils.data.distributed import DistributedSampler as TorchSampler
+    ds = list(range(103))
+    for world in (1, 2, 4):
+        for rank in range(world):
+            for shuffle in (False, True):
+                a = dtdl.DistributedSampler(ds, num_replicas=world, rank=rank, shuffle=shuffle, seed=3)
+                b = TorchSampler(ds, num_replicas=world, rank=rank, shuffle=shuffle, seed=3)
+                a.set_epoch(2)
+                b.set_epoch(2)
+                assert list(a) == list(b) and len(a) == len(b)
+
+
+def test_pyramidnet_structure():
+    w = pyramid_widths()
+    assert w[0] == 21 and w[-1] == 271 and len(w) == 51
+    m = pyramidnet()
+    assert sum(p.numel() for p in m.parameters()) == 24253410
+    assert len(list(m.parameters())) == 415 and len(list(m.buffers())) == 465
+    assert sum(p.numel() for p in MnistCNN().parameters()) == 93322
+    assert sum(p.numel() for p in MLP().parameters()) == 1796010
+
+
+def test_pyramidnet_matches_reference_definition():
+    """Same keys / shapes as the reference's model.py and identical output for its weights."""
+    import importlib.util
+    path = None
+    for cand in ("baseline/_ref/pytorch/model.py", "/root/reference/pytorch/model.py"):
+        if os.path.exists(cand):
+            path = cand
+            break
+    if path is None:
+        pytest.skip("reference model.py not available")
+    spec = importlib.util.spec_from_file_location("ref_model", path)
+    ref_mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref_mod)
+    torch.manual_seed(0)
+    ref = ref_mod.pyramidnet()
+    mine = pyramidnet()
+    assert list(ref.state_dict().keys()) == list(mine.state_dict().keys())
+    mine.load_state_dict(ref.state_dict())
+    x = torch.randn(3, 3, 32, 32)
+    ref.train()
+    mine.train()
+    assert torch.allclose(ref(x), mine(x), atol=1e-5)
+    ref.eval()
+    mine.eval()
+    assert torch.allclose(ref(x), mine(x), atol=1e-5)
+
+
+def _tiny():
+    return nn.Sequential(nn.Linear(12, 16), nn.ReLU(), nn.Linear(16, 5))
+
+
+@pytest.mark.parametrize("kind", ["sgd", "sgd_damp", "adam", "adam_wd"])
+def test_fused_optimizers_match_torch(kind):
+    torch.manual_seed(0)
+    a, b = _tiny(), None
+    b = copy.deepcopy(a)
+    if kind.startswith("sgd"):
+        kw = dict(lr=0.1, momentum=0.9, weight_decay=1e-4, dampening=0.1 if kind == "sgd_damp" else 0.0)
+        oa, ob = dtdl.FusedSGD(a.parameters(), **kw), torch.optim.SGD(b.parameters(), **kw)
+    else:
+        kw = dict(lr=1e-2, weight_decay=1e-2 if kind == "adam_wd" else 0.0)
+        oa, ob = dtdl.FusedAdam(a.parameters(), **kw), torch.optim.Adam(b.parameters(), **kw)
+    sched_a = torch.optim.lr_scheduler.StepLR(oa, step_size=2, gamma=0.1)
+    sched_b = torch.optim.lr_scheduler.StepLR(ob, step_size=2, gamma=0.1)
+    for step in range(5):
+        x, t = torch.randn(8, 12), torch.randint(0, 5, (8,))
+        for m, o, s in ((a, oa, sched_a), (b, ob, sched_b)):
+            loss = F.cross_entropy(m(x), t)
+            o.zero_grad()
+            loss.backward()
+            o.step()
+            s.step()
+    for pa, pb in zip(a.parameters(), b.parameters()):
+        assert torch.allclose(pa, pb, atol=1e-6), kind
+    sa, sb = oa.state_dict(), ob.state_dict()
+    key = "momentum_buffer" if kind.startswith("sgd") else "exp_avg"
+    assert set(sa["state"].keys()) == set(sb["state"].keys())
+    for i in sb["state"]:
+        assert torch.allclose(sa["state"][i][key], sb["state"][i][key], atol=1e-6)
+    # resume: a fresh optimizer continues identically from the state dict
+    c = copy.deepcopy(a)
+    oc = type(oa)(c.parameters(), **kw)
+    oc.load_state_dict(sa)
+    x, t = torch.randn(8, 12), torch.randint(0, 5, (8,))
+    for m, o in ((a, oa), (c, oc)):
+        loss = F.cross_entropy(m(x), t)
+        o.zero_grad()
+        loss.backward()
+        o.step()
+    for pa, pc in zip(a.parameters(), c.parameters()):
+        assert torch.allclose(pa, pc, atol=1e-7)
+
+
+def test_keras_adam_first_step():
+    p = nn.Parameter(torch.tensor([1.0, -2.0]))
+    o = dtdl.FusedAdam([p], lr=1e-3, keras=True)
+    p.grad = torch.tensor([0.5, -0.25])
+    o.step()
+    # first Adam step moves every coordinate by ~lr against the gradient sign
+    assert torch.allclose(p.detach(), torch.tensor([1.0 - 1e-3, -2.0 + 1e-3]), atol=1e-6)
+
+
+def test_wrap_single_process_cpu(tmp_path):
+    """world_size 1: wrapper keys, fused step == torch SGD, checkpoint round trips."""
+    torch.manual_seed(0)
+    base = MLP(n_units=32)
+    ref = copy.deepcopy(base)
+    net = dtdl.wrap(base)
+    assert list(net.state_dict().keys()) == ["module." + k for k in ref.state_dict().keys()]
+    assert list(net.module.state_dict().keys()) == list(ref.state_dict().keys())
+    opt = dtdl.FusedSGD(net.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    ropt = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
+    for _ in range(3):
+        x, t = torch.randn(16, 784), torch.randint(0, 10, (16,))
+        out = net(x)
+        loss = F.cross_entropy(out, t)
+        opt.zero_grad()          # between forward and backward, as the reference does (R11)
+        loss.backward()
+        opt.step()
+        rl = F.cross_entropy(ref(x), t)
+        ropt.zero_grad()
+        rl.backward()
+        ropt.step()
+    for a, b in zip(net.module.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, atol=1e-6)
+    # checkpoints: wrapper spelling and bare spelling load into either kind of model
+    p1 = dtdl.save_model(net, str(tmp_path / "a" / "wrapped.pth"))
+    p2 = dtdl.save_model(net.module, str(tmp_path / "bare.pth"))
+    fresh = MLP(n_units=32)
+    dtdl.load_model(fresh, p1)
+    dtdl.load_model(net, p2)
+    for a, b in zip(fresh.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, atol=1e-6)
+    # full snapshot resume
+    sched = torch.optim.lr_scheduler.StepLR(opt, 2, 0.1)
+    snap = dtdl.save_snapshot(str(tmp_path / "snap.pt"), net, opt, sched, epoch=3)
+    net2 = dtdl.wrap(MLP(n_units=32))
+    opt2 = dtdl.FusedSGD(net2.parameters(), lr=0.5)
+    sched2 = torch.optim.lr_scheduler.StepLR(opt2, 2, 0.1)
+    info = dtdl.load_snapshot(snap, net2, opt2, sched2)
+    assert info["epoch"] == 3 and opt2.param_groups[0]["momentum"] == 0.9
+    for a, b in zip(net2.module.parameters(), net.module.parameters()):
+        assert torch.equal(a, b)
+
+
+def test_wrap_with_torch_optimizer_cpu():
+    torch.manual_seed(0)
+    base = MnistCNN()
+    ref = copy.deepcopy(base)
+    net = dtdl.wrap(base)
+    opt = torch.optim.Adam(net.parameters())
+    ropt = torch.optim.Adam(ref.parameters())
+    for _ in range(2):
+        x, t = torch.randn(4, 1, 28, 28), torch.randint(0, 10, (4,))
+        loss = F.cross_entropy(net(x), t)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        rl = F.cross_entropy(ref(x), t)
+        ropt.zero_grad()
+        rl.backward()
+        ropt.step()
+    for a, b in zip(net.module.parameters(), ref.parameters()):
+        assert torch.allclose(a, b, atol=1e-6)

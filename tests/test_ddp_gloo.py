@@ -1,0 +1,23 @@
+"""Multi-process plumbing on CPU (gloo, world_size 2): SURVEY.md section 4, test plan item 1."""
+import os
+
+import pytest
+
+import distributed_training_dl_b200 as dtdl
+from distributed_training_dl_b200.utils import free_port
+
+from _workers import ddp_equivalence, ddp_pyramidnet
+
+
+@pytest.mark.parametrize("init_kind", ["tcp", "env"])
+def test_ddp_equivalence_gloo(tmp_path, init_kind):
+    world = 2
+    dtdl.spawn(ddp_equivalence, nprocs=world, args=(world, init_kind, free_port(), str(tmp_path)),
+               set_env=(init_kind == "env"))
+    assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
+
+
+def test_ddp_pyramidnet_gloo(tmp_path):
+    world = 2
+    dtdl.spawn(ddp_pyramidnet, nprocs=world, args=(world, free_port(), str(tmp_path)), set_env=False)
+    assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
