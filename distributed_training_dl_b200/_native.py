@@ -98,10 +98,31 @@ def check(rc):
         raise NativeError(msg.decode() if msg else f"native call failed with code {rc}")
 
 
+# kernels launched per native call (everything not listed launches none)
+_LAUNCHES = {"conv_fprop": 1, "conv_wgrad": 2, "pack_weights": 1, "nchw_to_nhwc_bf16": 1, "bn_stats": 1,
+             "bn_apply": 1, "bn_bwd": 2, "relu_bwd": 1, "add_bf16": 1, "add_prefix_bf16": 1, "pool_fwd": 1,
+             "pool_bwd": 1, "subsample2": 1, "gap_fwd": 1, "gap_bwd": 1, "softmax_ce": 1, "colsum": 1,
+             "f32_to_bf16_pad": 1, "bf16_to_f32_unpad": 1, "comm_barrier": 1, "comm_allreduce": 1,
+             "comm_reduce_update": 1, "comm_broadcast": 1, "comm_allgather": 1, "local_update": 1}
+_launch_count = 0
+
+
+def reset_launch_count():
+    global _launch_count
+    _launch_count = 0
+
+
+def launch_count():
+    """Number of this library's kernels launched since ``reset_launch_count()``."""
+    return _launch_count
+
+
 def call(name, *args):
     """Calls ``dtdl_<name>`` and raises NativeError on a non-zero return code."""
+    global _launch_count
     fn = getattr(lib(), "dtdl_" + name)
     check(fn(*args))
+    _launch_count += _LAUNCHES.get(name, 0)
 
 
 def ptr(t):

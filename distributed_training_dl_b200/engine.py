@@ -1,0 +1,121 @@
+"""Training-step engine: one call = H2D copy, forward, loss, backward, reduce+update.
+
+``TrainStep(model, optimizer, criterion)`` is the user-facing fast path.  The reference's hot
+loop (pytorch/single_gpu.py:93-116) launches ~1500 tiny kernels per step from Python and blocks
+on three ``.item()`` calls; here the whole step -- including the side-stream bucket
+reductions and the fused optimizer -- is captured ONCE into a CUDA graph and replayed, inputs
+are copied from pinned host memory into static device buffers, and loss / accuracy counters
+stay on the device until the caller asks.  No tracing compiler is involved: capture records the
+hand-written kernels exactly as eager mode launches them.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import _native as nv
+from .ops import functional as fn
+
+
+class CrossEntropyLoss(nn.Module):
+    """Softmax cross entropy (mean) with the accuracy count folded into the same kernel
+    (K-O13 + K-O17; the reference: ``nn.CrossEntropyLoss`` + ``outputs.max(1)`` / ``eq`` /
+    ``sum`` -- pytorch/single_gpu.py:70,99,105-108).  ``last_stats`` = [loss, #correct]."""
+
+    def __init__(self):
+        super().__init__()
+        self.last_stats = None
+
+    def forward(self, logits, targets):
+        if not logits.is_cuda:
+            self.last_stats = None
+            return F.cross_entropy(logits, targets)
+        loss, stats = fn.softmax_cross_entropy(logits, targets)
+        self.last_stats = stats
+        return loss
+
+
+class TrainStep:
+    """Callable training step.
+
+    >>> step = TrainStep(net, opt, criterion)           # net = dtdl.wrap(model)
+    >>> loss = step(x_pinned_cpu, y_pinned_cpu)         # device scalar; .item() when needed
+
+    ``graph=True`` captures after ``warmup`` eager iterations (which also train).  Batch shape
+    must stay fixed once captured; a differently shaped batch falls back to eager for that call.
+    """
+
+    def __init__(self, model, optimizer, criterion=None, graph=True, warmup=3):
+        self.model, self.optimizer = model, optimizer
+        self.criterion = criterion if criterion is not None else CrossEntropyLoss()
+        self.device = next(model.parameters()).device
+        self.use_graph = graph and self.device.type == "cuda"
+        self.warmup = warmup
+        self._graph = None
+        self._calls = 0
+        self._done = None
+        self._sx = self._st = self._loss = self._stats = None
+        self.launches_per_step = None
+
+    # ------------------------------------------------------------------
+    def _eager(self, x, t):
+        out = self.model(x)
+        loss = self.criterion(out, t)
+        self.optimizer.zero_grad()
+        loss.backward()
+        self.optimizer.step()
+        return loss, getattr(self.criterion, "last_stats", None)
+
+    def _stage(self, x, t):
+        if self._sx is None or self._sx.shape != x.shape or self._st.shape != t.shape:
+            self._sx = torch.empty(x.shape, dtype=x.dtype, device=self.device)
+            self._st = torch.empty(t.shape, dtype=t.dtype, device=self.device)
+            self._graph = None
+            self._calls = 0
+        self._sx.copy_(x, non_blocking=True)
+        self._st.copy_(t, non_blocking=True)
+
+    def _capture(self):
+        opt = self.optimizer
+        nv.reset_launch_count()
+        g = torch.cuda.CUDAGraph()
+        step_before = getattr(opt, "_step", None)
+        with torch.cuda.graph(g):
+            loss, stats = self._eager(self._sx, self._st)
+        if step_before is not None:
+            opt._step = step_before  # capture does not execute; replays advance the counter
+        self.launches_per_step = nv.launch_count()
+        self._graph, self._loss, self._stats = g, loss, stats
+
+    def __call__(self, x, t):
+        if not self.use_graph:
+            if x.device != self.device:
+                x, t = x.to(self.device, non_blocking=True), t.to(self.device, non_blocking=True)
+            loss, self._stats = self._eager(x, t)
+            return loss
+        self._stage(x, t)
+        if self._graph is None:
+            if self._calls < self.warmup:
+                self._calls += 1
+                loss, self._stats = self._eager(self._sx, self._st)
+                return loss
+            torch.cuda.synchronize(self.device)
+            self._capture()
+        opt = self.optimizer
+        if hasattr(opt, "refresh_hyper"):
+            if getattr(opt, "hyper_changes_every_step", False) and self._done is not None:
+                self._done.synchronize()  # the previous replay must have read its values
+            opt.refresh_hyper(enqueue_copy=False)  # the graph re-reads the pinned block
+        self._graph.replay()
+        if getattr(opt, "hyper_changes_every_step", False):
+            self._done = torch.cuda.Event()
+            self._done.record()
+        if hasattr(opt, "_step"):
+            opt._step += 1
+        return self._loss
+
+    @property
+    def last_stats(self):
+        """Device tensor [loss, #correct] of the last step (``CrossEntropyLoss`` criterion)."""
+        return self._stats

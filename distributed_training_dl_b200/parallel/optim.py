@@ -227,6 +227,7 @@ class FusedAdam(_FusedBase):
     (tensorflow2/mnist_single.py:78); otherwise torch / Chainer's (chainer/train_mnist.py:69)."""
     opt_code = OPT_ADAM
     state_names = ("exp_avg", "exp_avg_sq")
+    hyper_changes_every_step = True  # bias corrections
 
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=None, weight_decay=0.0, keras=False):
         eps = (1e-7 if keras else 1e-8) if eps is None else eps
