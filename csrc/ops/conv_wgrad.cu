@@ -298,3 +298,65 @@ extern "C" int dtdl_conv_wgrad(const void* x, const void* dy, float* dw, void* w
   DTDL_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// ---------------------------------------------------------------------------
+// Weight gradient for callers that cannot allocate device memory.
+//
+// dtdl_conv_wgrad needs a split-K scratch buffer, and normally the caller
+// allocates it.  Some callers have no way to do that: a host program whose own
+// memory pool has already claimed the whole GPU, a plug-in that is handed
+// tensors but no allocator, or code that is entered while a stream is being
+// captured, where cudaMalloc is not permitted.  For them the scratch lives
+// inside this library, in the fixed-size array below.  The price is that every
+// GPU that loads the library carries these 32 MiB until the process exits, and
+// that problems needing more scratch than that are refused.
+//
+// Inside host code `g_wgrad_static_scratch` is only the host-side handle of the
+// symbol, not an address a kernel can use, so the device address is looked up
+// with cudaGetSymbolAddress -- once per device, with that device current -- and
+// that pointer is what the kernels receive.
+//
+// What a caller needs to know:
+//   * The first call on each device performs that look-up.  Make it before any
+//     stream capture begins on that device (a plain warm-up call is enough).
+//   * The call itself allocates nothing: no cudaMalloc / cudaFree, no library
+//     routine that allocates.  Inputs and the output gradient are the caller's.
+//   * All calls on a device share the one array and it keeps whatever the last
+//     call left in it.  Nothing in it has to start at zero: every partial sum
+//     the reduction pass reads was written earlier in the same call.  Because
+//     of the sharing, two calls that may run on the GPU at the same time
+//     (different streams, no dependency between them) race; keep them ordered.
+//   * Shapes whose scratch need (dtdl_conv_wgrad_workspace_bytes) exceeds
+//     dtdl_conv_wgrad_static_scratch_bytes() = 32 MiB are rejected with an error
+//     and nothing is launched.
+static constexpr long long kStaticScratchBytes = 32ll << 20;
+static __device__ __align__(256) unsigned char g_wgrad_static_scratch[kStaticScratchBytes];
+
+extern "C" long long dtdl_conv_wgrad_static_scratch_bytes(void) { return kStaticScratchBytes; }
+
+extern "C" int dtdl_conv_wgrad_static(const void* x, const void* dy, float* dw, int N, int H, int W,
+                                      int Cin, int Cin_p, int Ho, int Wo, int Cout, int Cout_p,
+                                      int KH, int KW, int pad_h, int pad_w, int accumulate,
+                                      void* stream_) {
+  static void* scratch_of_device[64] = {nullptr};
+  int dev = 0;
+  DTDL_CHECK_CUDA(cudaGetDevice(&dev));
+  DTDL_REQUIRE(dev >= 0 && dev < 64, "device index out of range for the static scratch table");
+  if (scratch_of_device[dev] == nullptr) {
+    // first call on this device: resolve the device address of the array
+    void* p = nullptr;
+    DTDL_CHECK_CUDA(cudaGetSymbolAddress(&p, g_wgrad_static_scratch));
+    DTDL_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    scratch_of_device[dev] = p;
+  }
+  const long long need = dtdl_conv_wgrad_workspace_bytes(N, Ho, Wo, Cin_p, Cout_p, KH, KW);
+  if (need > kStaticScratchBytes) {
+    set_last_error("dtdl_conv_wgrad_static: this shape needs " + std::to_string(need) +
+                   " bytes of scratch but the built-in buffer holds " +
+                   std::to_string(kStaticScratchBytes) +
+                   "; use dtdl_conv_wgrad with a caller-provided workspace");
+    return 3;
+  }
+  return dtdl_conv_wgrad(x, dy, dw, scratch_of_device[dev], kStaticScratchBytes, N, H, W, Cin, Cin_p,
+                         Ho, Wo, Cout, Cout_p, KH, KW, pad_h, pad_w, accumulate, stream_);
+}

@@ -43,6 +43,20 @@ int dtdl_conv_wgrad(const void* x, const void* dy, float* dw, void* workspace,
                     int Wo, int Cout, int Cout_p, int KH, int KW, int pad_h, int pad_w,
                     int accumulate, void* stream);
 
+/* dtdl_conv_wgrad for callers that cannot allocate device memory (no counterpart in the
+ * reference, which never manages scratch itself).  Such callers exist: programs whose own pool
+ * owns all GPU memory, plug-ins that receive tensors but no allocator, code entered during
+ * stream capture where cudaMalloc is not allowed.  The split-K scratch is a 32 MiB array
+ * inside the library (held by every GPU that loads it until exit); shapes needing more are
+ * rejected.  Same arguments and result as dtdl_conv_wgrad minus the workspace pair.  The first
+ * call on a device resolves the array's device address -- make it before any stream capture.
+ * Calls share the array: calls that can overlap on the GPU race, so keep them stream-ordered.
+ * The call allocates nothing. */
+long long dtdl_conv_wgrad_static_scratch_bytes(void);
+int dtdl_conv_wgrad_static(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin,
+                           int Cin_p, int Ho, int Wo, int Cout, int Cout_p, int KH, int KW,
+                           int pad_h, int pad_w, int accumulate, void* stream);
+
 /* fp32 master weights -> bf16 operand packs for a whole model in one launch. */
 int dtdl_pack_entry_size(void);
 long long dtdl_pack_entry_fill(void* entry, const float* w, void* wf, void* wd, int Cout, int Cin,
