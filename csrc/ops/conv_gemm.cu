@@ -48,7 +48,7 @@ struct ConvGemmArgs {
 
 static constexpr int kAStage = 128 * 128;  // 128 pixel rows x 64 bf16
 
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(256, 2)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const ConvGemmArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -260,7 +260,11 @@ extern "C" int dtdl_conv_fprop(const void* x, const void* wpack, void* y, const 
   a.tmem_cols = n_tile <= 32 ? 32 : n_tile <= 64 ? 64 : n_tile <= 128 ? 128 : 256;
   a.b_stage_bytes = (n_tile * 128 + 1023) / 1024 * 1024;
   const int stage_bytes = kAStage + a.b_stage_bytes;
-  int stages = (200 * 1024) / stage_bytes;
+  // Many small tiles: keep shared memory under half an SM so two CTAs are resident and one
+  // tile's epilogue overlaps the other's main loop.  Few big tiles: one deep pipeline.
+  const bool two_per_sm = (long long)m_tiles * n_tiles > sm_count() && 3 * stage_bytes <= 110 * 1024 &&
+                          a.tmem_cols <= 256;
+  int stages = ((two_per_sm ? 110 : 200) * 1024) / stage_bytes;
   if (stages > 8) stages = 8;
   const int n_kblocks = a.taps * a.chunks;
   if (stages > n_kblocks) stages = n_kblocks < 2 ? 2 : n_kblocks;

@@ -186,19 +186,57 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constan
 }
 
 // dw[co][ci][t] (OIHW, fp32) = (accumulate ? dw : 0) + sum_split ws[split][t][co][ci]
-__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw,
-                                    int splits, int taps, int Cout, int Cin, int Cout_p, int Cin_w,
-                                    int accumulate) {
-  const int ci = blockIdx.x * blockDim.x + threadIdx.x;
+// Block = 64 (tap, 4-channel vector) items x 4 split lanes; every lane sums its
+// splits (s = lane, lane+4, ...) with float4 loads, the four lanes are combined
+// through shared memory in a fixed order, so the result does not depend on timing.
+__global__ void __launch_bounds__(256)
+wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int splits, int taps,
+                    int Cout, int Cin, int Cout_p, int Cin_w, int accumulate) {
+  __shared__ float4 part[4][64];
+  const int item = blockIdx.x * 64 + (threadIdx.x & 63);
+  const int lane = threadIdx.x >> 6;
   const int co = blockIdx.y;
-  if (ci >= Cin) return;
-  for (int t = 0; t < taps; ++t) {
-    float acc = 0.f;
-    const float* p = ws + ((size_t)t * Cout_p + co) * Cin_w + ci;
-    const size_t stride = (size_t)taps * Cout_p * Cin_w;
-    for (int s = 0; s < splits; ++s) acc += p[s * stride];
-    float* o = dw + ((size_t)co * Cin + ci) * taps + t;
-    *o = accumulate ? (*o + acc) : acc;
+  const int vec_per_tap = Cin_w >> 2;
+  const int n_items = taps * vec_per_tap;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int t = item / vec_per_tap, c4 = item % vec_per_tap;
+  if (item < n_items) {
+    const size_t stride4 = ((size_t)taps * Cout_p * Cin_w) >> 2;
+    const float4* p = reinterpret_cast<const float4*>(ws + ((size_t)t * Cout_p + co) * Cin_w) + c4;
+    int s = lane;
+    for (; s + 12 < splits; s += 16) {
+      const float4 v0 = p[(size_t)s * stride4];
+      const float4 v1 = p[(size_t)(s + 4) * stride4];
+      const float4 v2 = p[(size_t)(s + 8) * stride4];
+      const float4 v3 = p[(size_t)(s + 12) * stride4];
+      acc.x += (v0.x + v1.x) + (v2.x + v3.x);
+      acc.y += (v0.y + v1.y) + (v2.y + v3.y);
+      acc.z += (v0.z + v1.z) + (v2.z + v3.z);
+      acc.w += (v0.w + v1.w) + (v2.w + v3.w);
+    }
+    for (; s < splits; s += 4) {
+      const float4 v = p[(size_t)s * stride4];
+      acc.x += v.x;
+      acc.y += v.y;
+      acc.z += v.z;
+      acc.w += v.w;
+    }
+  }
+  part[lane][threadIdx.x & 63] = acc;
+  __syncthreads();
+  if (lane == 0 && item < n_items) {
+    const float4 a0 = part[0][threadIdx.x], a1 = part[1][threadIdx.x], a2 = part[2][threadIdx.x],
+                 a3 = part[3][threadIdx.x];
+    const float r[4] = {(a0.x + a1.x) + (a2.x + a3.x), (a0.y + a1.y) + (a2.y + a3.y),
+                        (a0.z + a1.z) + (a2.z + a3.z), (a0.w + a1.w) + (a2.w + a3.w)};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int ci = c4 * 4 + j;
+      if (ci < Cin) {
+        float* o = dw + ((size_t)co * Cin + ci) * taps + t;
+        *o = accumulate ? (*o + r[j]) : r[j];
+      }
+    }
   }
 }
 
@@ -292,8 +330,8 @@ extern "C" int dtdl_conv_wgrad(const void* x, const void* dy, float* dw, void* w
   conv_wgrad_kernel<<<grid, 256, smem, stream>>>(tmDy, tmX, a);
   DTDL_CHECK_CUDA(cudaGetLastError());
 
-  dim3 rgrid((Cin + 127) / 128, Cout);
-  wgrad_reduce_kernel<<<rgrid, 128, 0, stream>>>(a.ws, dw, splits, a.taps, Cout, Cin, Cout_p,
+  dim3 rgrid((a.taps * (a.Cin_w / 4) + 63) / 64, Cout);
+  wgrad_reduce_kernel<<<rgrid, 256, 0, stream>>>(a.ws, dw, splits, a.taps, Cout, Cin, Cout_p,
                                                  a.Cin_w, accumulate);
   DTDL_CHECK_CUDA(cudaGetLastError());
   return 0;
