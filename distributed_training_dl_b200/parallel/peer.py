@@ -178,8 +178,13 @@ class PeerComm:
     def allreduce(self, buf: SymmBuffer, offset_bytes: int, numel: int, scale: float = 1.0,
                   two_shot=None, dst: SymmBuffer = None, stream=None, max_blocks=None):
         """In-place (or into ``dst``) sum * scale of ``numel`` fp32 elements on every rank."""
+        in_place = dst is None or dst is buf
         dst = dst or buf
         ts = self.choose_two_shot(numel * 4) if two_shot is None else int(two_shot)
+        if in_place and self.world > 1:
+            # one-shot reads every rank's whole buffer, so it may not overwrite its source;
+            # two-shot only writes the slice that nobody else reads
+            ts = 1
         nv.call("comm_allreduce", self.handle, buf.ptr_array, dst.ptr_array, offset_bytes, numel, scale, ts,
                 max_blocks or self.max_blocks, self._stream(stream))
 

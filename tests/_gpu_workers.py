@@ -1,0 +1,152 @@
+"""Worker bodies for the multi-GPU tests (one process per GPU, peer-memory backend)."""
+import copy
+import os
+import sys
+
+import torch
+import torch.nn.functional as F
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def _ok(outdir, i):
+    open(os.path.join(outdir, f"ok_{i}"), "w").write("ok")
+
+
+def collectives(i, world, outdir):
+    import distributed_training_dl_b200 as dtdl
+    comm = dtdl.init(backend="b200")
+    peer = comm.peer
+    dev = comm.device
+    assert comm.rank == i and peer.world == world
+    n = 1 << 20
+    buf = peer.alloc(n * 4)
+    out = peer.alloc(n * 4)
+    x = buf.view(torch.float32, 0, n)
+    y = out.view(torch.float32, 0, n)
+    for numel, two_shot in [(256, 0), (4096, 0), (4096, 1), (n, 0), (n, 1), (n - 8, 1)]:
+        for rep in range(3):   # repeated iterations: cross-GPU races show up as flaky mismatches
+            g = torch.Generator(device="cpu").manual_seed(100 * rep + numel)
+            full = torch.randn(world, numel, generator=g)
+            x[:numel].copy_(full[i])
+            y.zero_()
+            peer.allreduce(buf, 0, numel, scale=1.0 / world, two_shot=two_shot, dst=out)
+            torch.cuda.synchronize()
+            want = full.sum(0) / world
+            assert torch.allclose(y[:numel].cpu(), want, atol=1e-5), (numel, two_shot, rep)
+            # in place (always runs the two-shot schedule: one-shot may not overwrite its source)
+            peer.allreduce(buf, 0, numel, scale=1.0)
+            torch.cuda.synchronize()
+            assert torch.allclose(x[:numel].cpu(), full.sum(0), atol=1e-5), ("inplace", numel, two_shot)
+            comm.barrier()
+    # bit-identical results on every rank (fixed reduction order)
+    x.copy_(torch.randn(n, generator=torch.Generator().manual_seed(i)))
+    peer.allreduce(buf, 0, n, two_shot=1)
+    torch.cuda.synchronize()
+    sums = comm.allgather_object(x[:4096].cpu())
+    assert all(torch.equal(sums[0], s) for s in sums)
+    # broadcast + all-gather
+    x.fill_(float(i + 1))
+    peer.broadcast(buf, 0, n * 4, root=world - 1)
+    torch.cuda.synchronize()
+    assert float(x.min()) == float(x.max()) == float(world)
+    per = n // world
+    x.zero_()
+    x[i * per:(i + 1) * per] = i + 1
+    peer.allgather(buf, 0, n * 4)
+    torch.cuda.synchronize()
+    for r in range(world):
+        assert float(x[r * per]) == r + 1 and float(x[(r + 1) * per - 1]) == r + 1
+    # fused all-reduce + SGD / Adam against the unfused torch arithmetic
+    for opt_code, two_shot in [(1, 0), (1, 1), (2, 1), (3, 0)]:
+        numel = 1 << 16
+        g = torch.Generator().manual_seed(7 + opt_code)
+        grads = torch.randn(world, numel, generator=g)
+        p0 = torch.randn(numel, generator=g)
+        params = peer.alloc(numel * 4)
+        p = params.view(torch.float32, 0, numel)
+        p.copy_(p0)
+        x[:numel].copy_(grads[i])
+        m = torch.zeros(numel, device=dev)
+        v = torch.zeros(numel, device=dev)
+        lr, mu, wd, b1, b2, eps = 0.1, 0.9, 1e-2, 0.9, 0.999, 1e-8
+        hyper = torch.tensor([lr, mu, wd, 1.0 / world, b1, b2, eps, 1 - b1, (1 - b2) ** 0.5, 0.0] + [0.0] * 6, device=dev)
+        if two_shot:
+            ms, vs = peer.alloc(numel * 4), peer.alloc(numel * 4)
+            m, v = ms.view(torch.float32, 0, numel), vs.view(torch.float32, 0, numel)
+        peer.reduce_update(buf, params, m, v, hyper, 0, numel, opt_code, two_shot=two_shot)
+        torch.cuda.synchronize()
+        gavg = grads.mean(0) + wd * p0
+        if opt_code == 1:
+            want = p0 - lr * gavg
+        else:
+            m1, v1 = (1 - b1) * gavg, (1 - b2) * gavg * gavg
+            if opt_code == 2:
+                want = p0 - lr / (1 - b1) * m1 / (v1.sqrt() / (1 - b2) ** 0.5 + eps)
+            else:
+                want = p0 - lr * (1 - b2) ** 0.5 / (1 - b1) * m1 / (v1.sqrt() + eps)
+        assert torch.allclose(p.cpu(), want, atol=2e-5), (opt_code, two_shot, (p.cpu() - want).abs().max())
+        allp = comm.allgather_object(p[:2048].cpu())
+        assert all(torch.equal(allp[0], q) for q in allp)
+    _ok(outdir, i)
+    dtdl.shutdown()
+
+
+def ddp_training(i, world, outdir, use_graph):
+    import distributed_training_dl_b200 as dtdl
+    from distributed_training_dl_b200.engine import CrossEntropyLoss, TrainStep
+    from distributed_training_dl_b200.models import MLP, PyramidNet
+    comm = dtdl.init(backend="b200")
+    dev = comm.device
+    torch.manual_seed(1 + i)
+    # (a) replicas identical after construction although seeded differently
+    net = dtdl.wrap(PyramidNet(num_layers=3, alpha=45.0).to(dev))
+    chk = torch.cat([p.detach().flatten()[:32] for p in net.parameters()]).cpu()
+    alls = comm.allgather_object(chk)
+    assert all(torch.equal(alls[0], a) for a in alls)
+    opt = dtdl.FusedSGD(net.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+    step = TrainStep(net, opt, CrossEntropyLoss(), graph=use_graph, warmup=2)
+    g = torch.Generator().manual_seed(5 + i)
+    losses = []
+    for it in range(8):
+        x = torch.randn(16, 3, 32, 32, generator=g).pin_memory()
+        t = torch.randint(0, 10, (16,), generator=g).pin_memory()
+        losses.append(step(x, t).item())
+    assert all(l == l for l in losses), losses
+    torch.cuda.synchronize()
+    # replicas stay bit-identical; running stats follow rank 0
+    chk = torch.cat([p.detach().flatten()[:64] for p in net.parameters()]).cpu()
+    alls = comm.allgather_object(chk)
+    assert all(torch.equal(alls[0], a) for a in alls), "replicas diverged"
+    # optimizer state in torch format after a sharded (two-shot) update
+    sd = opt.state_dict()
+    mb = comm.allgather_object(sd["state"][0]["momentum_buffer"].flatten()[:16].cpu())
+    assert all(torch.equal(mb[0], q) for q in mb)
+
+    # (c) MLP (no BN): k steps == single-process fp32 run on the concatenated batch
+    torch.manual_seed(3)
+    mlp = MLP(n_units=64)
+    ref = copy.deepcopy(mlp)
+    net2 = dtdl.wrap(mlp.to(dev))
+    opt2 = dtdl.FusedSGD(net2.parameters(), lr=0.05, momentum=0.9)
+    ropt = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9)
+    g = torch.Generator().manual_seed(11)
+    for it in range(3):
+        xs = torch.randn(world, 32, 784, generator=g)
+        ts = torch.randint(0, 10, (world, 32), generator=g)
+        loss = F.cross_entropy(net2(xs[i].to(dev)), ts[i].to(dev))
+        opt2.zero_grad()
+        loss.backward()
+        opt2.step()
+        rl = F.cross_entropy(ref(xs.reshape(-1, 784)), ts.reshape(-1))
+        ropt.zero_grad()
+        rl.backward()
+        ropt.step()
+    torch.cuda.synchronize()
+    for (n_, p), q in zip(net2.module.named_parameters(), ref.parameters()):
+        err = (p.detach().cpu() - q).abs().max().item()
+        assert err < 5e-3, (n_, err)
+    _ok(outdir, i)
+    dtdl.shutdown()

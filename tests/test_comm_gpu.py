@@ -1,0 +1,31 @@
+"""Peer-memory collectives and DDP-style training on >= 2 GPUs (skipped on a 1-GPU box)."""
+import os
+
+import pytest
+import torch
+
+import distributed_training_dl_b200 as dtdl
+
+from _gpu_workers import collectives, ddp_training
+
+pytestmark = pytest.mark.gpu
+
+
+def _world():
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs at least 2 GPUs")
+    return min(n, int(os.environ.get("DTDL_TEST_WORLD", "2")))
+
+
+def test_peer_collectives(tmp_path):
+    world = _world()
+    dtdl.spawn(collectives, nprocs=world, args=(world, str(tmp_path)))
+    assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
+
+
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_ddp_training(tmp_path, use_graph):
+    world = _world()
+    dtdl.spawn(ddp_training, nprocs=world, args=(world, str(tmp_path), use_graph))
+    assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
