@@ -91,11 +91,16 @@ def scratch(device, nbytes: int) -> torch.Tensor:
 # layout
 # --------------------------------------------------------------------------------------
 def to_nhwc(x: torch.Tensor, Cp: int | None = None) -> torch.Tensor:
-    """NCHW (or [N,F]) fp32 -> NHWC bf16 padded.  No gradient flows to the input."""
+    """NCHW (or [N,F]) fp32 -> NHWC bf16 padded.  No gradient flows to the input.
+
+    The result lives on the CURRENT device even when ``x`` is a (peer-accessible) tensor of
+    another GPU: the kernel then reads its batch slice over NVLink, which is how the
+    single-process engine folds ``scatter`` into the first layer (K-C4)."""
+    dev = torch.device("cuda", torch.cuda.current_device())
     if x.dim() == 2:
         N, C = x.shape
         Cp = Cp or pad8(C)
-        y = torch.empty((N, 1, 1, Cp), dtype=torch.bfloat16, device=x.device)
+        y = torch.empty((N, 1, 1, Cp), dtype=torch.bfloat16, device=dev)
         nv.call("f32_to_bf16_pad", nv.ptr(x.contiguous().float()), nv.ptr(y), N, C, Cp, nv.stream_ptr())
         return y
     N, C, H, W = x.shape
@@ -103,7 +108,7 @@ def to_nhwc(x: torch.Tensor, Cp: int | None = None) -> torch.Tensor:
     x = x.detach()
     if x.dtype != torch.float32 or not x.is_contiguous():
         x = x.contiguous().float()
-    y = torch.empty((N, H, W, Cp), dtype=torch.bfloat16, device=x.device)
+    y = torch.empty((N, H, W, Cp), dtype=torch.bfloat16, device=dev)
     nv.call("nchw_to_nhwc_bf16", nv.ptr(x), nv.ptr(y), N, C, H, W, Cp, nv.stream_ptr())
     return y
 
