@@ -8,26 +8,34 @@ schedulers (the reference uses ``StepLR``, pytorch/distributed_data_parallel.py:
 correction), Keras' epsilon placement is available for the TF2 examples
 (tensorflow2/mnist_single.py:78).
 
-When the model is wrapped (:func:`..wrap.wrap`), the update of a bucket runs inside the
-bucket's all-reduce kernel during backward, and ``step()`` only joins the communication stream,
-re-packs the bf16 weight operands and advances the step counter.  ``lr`` etc. are read from
-``param_groups`` every step (through a small device-side hyper-parameter block), never baked in.
+When the model is wrapped (``wrap`` / ``DataParallel``), the update of a bucket runs inside the
+bucket's all-reduce kernel, and ``step()`` only joins the communication stream, re-packs the
+bf16 weight operands and advances the step counter.  ``lr`` etc. are read from ``param_groups``
+every step (through a small device-side hyper-parameter block), never baked in.
+
+One optimizer object can drive several replicas (the single-process multi-GPU engine): state
+arenas, hyper-parameter blocks and weight-pack tables then exist once per GPU.
 """
 from __future__ import annotations
 
+import contextlib
 import math
 
 import torch
 
 from .. import _native as nv
-from ..ops import functional as fn
 
 OPT_SGD, OPT_ADAM, OPT_ADAM_KERAS = 1, 2, 3
+
+
+def _on(device):
+    return torch.cuda.device(device) if device.type == "cuda" else contextlib.nullcontext()
 
 
 class _FusedBase(torch.optim.Optimizer):
     opt_code = 0
     state_names = ()
+    hyper_changes_every_step = False
 
     def __init__(self, params, defaults):
         super().__init__(params, defaults)
@@ -35,11 +43,12 @@ class _FusedBase(torch.optim.Optimizer):
             raise ValueError("the fused optimizers support a single parameter group")
         self._step = 0
         self._reducer = None
-        self._arena = None
-        self._state_flat = {}
+        self._arenas = []          # one per replica this optimizer drives
+        self._states = []          # per replica: {state name: flat fp32 tensor}
         self._hyper_host = None
-        self._hyper_dev = None
-        self._pack_cache = {}
+        self._hyper_devs = []
+        self._pack_caches = []
+        self._own_packed = None
         arena = getattr(self._params()[0], "_dtdl_arena", None)
         if arena is not None and getattr(arena, "reducer", None) is not None:
             self.attach(arena.reducer)  # optimizer built after wrap(), as the reference does
@@ -49,56 +58,86 @@ class _FusedBase(torch.optim.Optimizer):
         return [p for p in self.param_groups[0]["params"] if p.requires_grad]
 
     def attach(self, reducer):
-        """Called by ``wrap``: the reducer owns the arenas this optimizer updates."""
+        """Called by ``wrap`` / ``DataParallel``: the reducer owns the arenas this optimizer updates."""
         self._reducer = reducer
-        self._bind_arena(reducer.arena)
+        arenas = getattr(reducer, "arenas", None) or [reducer.arena]
+        self._bind(arenas)
         reducer.optimizer = self
 
-    def _bind_arena(self, arena):
-        self._arena = arena
-        dev = arena.device
-        symmetric = arena.peer is not None and arena.peer.world > 1
-        for name in self.state_names:
-            self._state_flat[name] = arena.new_state(symmetric=symmetric)
+    def _bind(self, arenas):
+        self._arenas = list(arenas)
+        self._states, self._hyper_devs, self._pack_caches = [], [], []
         self._hyper_host = torch.zeros(16, dtype=torch.float32)
-        if dev.type == "cuda":
+        if self._arenas[0].device.type == "cuda":
             self._hyper_host = self._hyper_host.pin_memory()
-            self._hyper_dev = torch.zeros(16, dtype=torch.float32, device=dev)
+        for a in self._arenas:
+            multi_proc = (a.peer is not None and a.peer.world > 1
+                          and getattr(a.peer, "_local_group", None) is None)
+            with _on(a.device):
+                self._states.append({n: a.new_state(symmetric=multi_proc) for n in self.state_names})
+                self._hyper_devs.append(torch.zeros(16, dtype=torch.float32, device=a.device)
+                                        if a.device.type == "cuda" else None)
+            self._pack_caches.append({})
         self.refresh_hyper()
 
     def _ensure_arena(self):
-        if self._arena is None:
+        if not self._arenas:
             from .arena import ParamArena
             params = self._params()
             arena = getattr(params[0], "_dtdl_arena", None)
             if arena is None:
                 arena = ParamArena(params, params[0].device)
-            self._bind_arena(arena)
+            self._bind([arena])
+
+    # single-replica aliases used by the multi-process reducer
+    @property
+    def _arena(self):
+        return self._arenas[0] if self._arenas else None
+
+    @property
+    def _state_flat(self):
+        return self._states[0]
+
+    @property
+    def _hyper_dev(self):
+        return self._hyper_devs[0]
+
+    def _state_on(self, g):
+        st = self._states[g]
+        return st[self.state_names[0]], (st[self.state_names[1]] if len(self.state_names) > 1 else None)
+
+    def _hyper_on(self, g):
+        return self._hyper_devs[g]
 
     # ------------------------------------------------------------------ hyper-parameters
     def _hyper_values(self, world):
         raise NotImplementedError
 
+    def _world(self):
+        r = self._reducer
+        return getattr(r, "world", 1) if r is not None else 1
+
     def refresh_hyper(self, enqueue_copy=True):
         """Writes the current ``param_groups`` values into the pinned block and (optionally)
-        enqueues its copy to the device.  A captured CUDA graph re-reads the pinned block on
+        enqueues its copy to the device(s).  A captured CUDA graph re-reads the pinned block on
         every replay, so calling this with ``enqueue_copy=False`` before a replay is enough."""
-        world = self._reducer.world if self._reducer is not None else 1
-        vals = self._hyper_values(world)
+        vals = self._hyper_values(self._world())
         self._hyper_host[: len(vals)] = torch.tensor(vals, dtype=torch.float32)
-        if self._hyper_dev is not None and enqueue_copy:
-            self._hyper_dev.copy_(self._hyper_host, non_blocking=True)
+        if enqueue_copy:
+            for h in self._hyper_devs:
+                if h is not None:
+                    with torch.cuda.device(h.device):
+                        h.copy_(self._hyper_host, non_blocking=True)
 
     # ------------------------------------------------------------------ step
     def zero_grad(self, set_to_none: bool = True):
         """No memset for kernel-written gradients: the next backward overwrites them (see
         ops.functional.grad_buffer).  Gradients produced by stock torch ops are dropped."""
-        for p in self._params():
-            if getattr(p, "_dtdl_native", False):
-                p._dtdl_fresh = True
-            else:
+        plist = self._params() if len(self._arenas) <= 1 else [p for a in self._arenas for p in a.params]
+        for p in plist:
+            if not getattr(p, "_dtdl_native", False):
                 p.grad = None
-                p._dtdl_fresh = True
+            p._dtdl_fresh = True
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -113,46 +152,75 @@ class _FusedBase(torch.optim.Optimizer):
                     g.copy_(p.grad)
                     p.grad = g
             self.refresh_hyper()
-            self._local_update()
+            self._local_update_on(0)
         self._step += 1
         self._repack()
         return loss
 
-    def _local_update(self):
-        a = self._arena
+    def _local_update_on(self, g):
+        a = self._arenas[g]
         if a.device.type == "cuda":
-            m = self._state_flat[self.state_names[0]]
-            v = self._state_flat[self.state_names[1]] if len(self.state_names) > 1 else None
-            nv.call("local_update", nv.ptr(a.param_flat), nv.ptr(a.grad_flat), nv.ptr(m), nv.ptr(v),
-                    nv.ptr(self._hyper_dev), a.numel, self.opt_code, nv.stream_ptr())
+            m, v = self._state_on(g)
+            with torch.cuda.device(a.device):
+                nv.call("local_update", nv.ptr(a.param_flat), nv.ptr(a.grad_flat), nv.ptr(m), nv.ptr(v),
+                        nv.ptr(self._hyper_devs[g]), a.numel, self.opt_code,
+                        torch.cuda.current_stream(a.device).cuda_stream)
         else:
             self._update_torch(a.grad_flat, 0, a.numel)
+
+    def _local_update(self):
+        self._local_update_on(0)
 
     def _update_torch(self, grad_flat, off, n):
         raise NotImplementedError
 
     def _repack(self):
         """bf16 operand packs of conv / linear weights follow the fp32 master weights."""
-        if self._arena.device.type != "cuda":
+        if self._arenas[0].device.type != "cuda":
             return
-        mods = self._reducer.packed_modules if self._reducer is not None else self._pack_cache.get("mods")
+        from ..ops.modules import pack_weights
+        r = self._reducer
+        if r is not None and hasattr(r, "repack_all"):
+            r.repack_all(self._pack_caches)
+            return
+        mods = r.packed_modules if r is not None else self._own_packed
         if mods:
-            from ..ops.modules import pack_weights
-            pack_weights(mods, self._pack_cache)
+            pack_weights(mods, self._pack_caches[0])
 
     def register_packed_modules(self, module):
+        """Bare (unwrapped) model: tell the optimizer which layers need re-packing after a step."""
         from ..ops.modules import packed_layers
-        self._pack_cache = {"mods": packed_layers(module)}
+        self._own_packed = packed_layers(module)
 
     # ------------------------------------------------------------------ torch-format state
     def _gather_state(self):
+        """Two-shot fused updates shard the optimizer state by rank; make replica 0's copy whole."""
         red = self._reducer
-        if red is not None and red.world > 1 and red.peer is not None and self._step > 0:
-            for t in self._state_flat.values():
+        if red is None or self._step == 0 or not getattr(red, "state_sharded", False):
+            return
+        a0 = self._arenas[0]
+        if len(self._arenas) > 1:        # single process: copy each owner's slice over
+            W = len(self._arenas)
+            for name in self.state_names:
+                for b in a0.buckets:
+                    if not a0.peer.choose_two_shot(b.numel * 4):
+                        continue
+                    n4 = b.numel // 4
+                    per = (n4 + W - 1) // W
+                    for r in range(1, W):
+                        lo, hi = b.offset + 4 * per * r, b.offset + 4 * min(per * (r + 1), n4)
+                        if hi > lo:
+                            self._states[0][name][lo:hi].copy_(self._states[r][name][lo:hi])
+        elif getattr(red, "peer", None) is not None and red.world > 1:
+            for t in self._states[0].values():
                 buf = getattr(t, "_dtdl_symm", None)
-                if buf is not None and red.state_sharded:
-                    red.peer.allgather(buf, 0, self._arena.numel * 4)
-            torch.cuda.synchronize(self._arena.device)
+                if buf is None:
+                    continue
+                for b in a0.buckets:
+                    if red.peer.choose_two_shot(b.numel * 4):
+                        red.peer.allgather(buf, b.offset * 4, b.numel * 4)
+        if a0.device.type == "cuda":
+            torch.cuda.synchronize(a0.device)
 
     def state_dict(self):
         self._ensure_arena()
@@ -163,7 +231,7 @@ class _FusedBase(torch.optim.Optimizer):
             for i, p in enumerate(params):
                 if not p.requires_grad:
                     continue
-                entry = {k: self._arena.flat_view_like(t, p).clone() for k, t in self._state_flat.items()}
+                entry = {k: self._arena.flat_view_like(t, p).clone() for k, t in self._states[0].items()}
                 entry.update(self._extra_state())
                 state[i] = entry
         group = {k: v for k, v in self.param_groups[0].items() if k != "params"}
@@ -176,13 +244,16 @@ class _FusedBase(torch.optim.Optimizer):
         g = dict(sd["param_groups"][0])
         g.pop("params", None)
         self.param_groups[0].update(g)
-        for t in self._state_flat.values():
-            t.zero_()
+        for st in self._states:
+            for t in st.values():
+                t.zero_()
         for i, entry in sd.get("state", {}).items():
             p = params[int(i)]
-            for k, t in self._state_flat.items():
-                if k in entry:
-                    self._arena.flat_view_like(t, p).copy_(entry[k])
+            off = self._arenas[0].offsets[id(p)]
+            for st in self._states:
+                for k, t in st.items():
+                    if k in entry:
+                        t[off: off + p.numel()].copy_(entry[k].reshape(-1))
         steps = [int(e["step"]) for e in sd.get("state", {}).values() if "step" in e]
         self._step = int(sd.get("dtdl_step", max(steps) if steps else (1 if sd.get("state") else 0)))
         self.refresh_hyper()
@@ -231,10 +302,10 @@ class FusedAdam(_FusedBase):
 
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=None, weight_decay=0.0, keras=False):
         eps = (1e-7 if keras else 1e-8) if eps is None else eps
-        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
         self.keras = keras
         if keras:
             self.opt_code = OPT_ADAM_KERAS
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay))
 
     def _hyper_values(self, world):
         g = self.param_groups[0]
