@@ -227,6 +227,8 @@ class OutputLayout(nn.Module):
     def forward(self, x):
         if not is_native(x):
             return x.reshape(x.shape[0], -1)
+        if getattr(self, "_bypass", False):
+            return x  # the single-process engine converts while gathering to GPU 0
         return fn.to_f32(x, self.features)
 
 

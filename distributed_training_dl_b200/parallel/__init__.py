@@ -4,3 +4,4 @@ from .rendezvous import (Communicator, RendezvousSpec, create_communicator, curr
                          expand_slurm_nodelist, init, resolve_spec, shutdown, spec_from_env,
                          spec_from_hosts, spec_from_slurm)
 from .wrap import DistributedDataParallel, DistributedModel, Reducer, wrap
+from .data_parallel import DataParallel, DataParallelStep

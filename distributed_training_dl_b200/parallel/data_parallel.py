@@ -1,0 +1,332 @@
+"""Single-process, multi-GPU data parallelism (``nn.DataParallel`` / ``MirroredStrategy`` style).
+
+The reference's ``nn.DataParallel`` (pytorch/data_parallel.py:70-72) re-broadcasts all 92 MB of
+parameters from GPU 0 at EVERY forward, scatters the input, runs one Python thread per GPU,
+gathers logits and reduces all gradients onto GPU 0, which alone runs the optimizer
+(SURVEY.md section 3.2).  This engine keeps the call contract -- input on GPU 0, logits on
+GPU 0, ``.module`` is the original model, ``state_dict()`` keys carry ``module.`` -- but:
+
+* replicas are persistent; the fused reducer updates every replica's parameters identically,
+  so the per-step parameter broadcast (K-C5) does not exist;
+* scatter is folded into each replica's first kernel, which reads its batch slice from GPU 0's
+  input tensor over NVLink (K-C4); gather is folded into the last kernel, which writes fp32
+  logits (or adds its share of the loss) straight into GPU 0's memory (K-C6);
+* gradients are reduced by the same peer-memory fused all-reduce + optimizer kernels as the
+  multi-process path (K-C7), one launch per bucket per GPU, instead of reduce-to-GPU-0;
+* one thread drives all GPUs: :class:`DataParallelStep` replays ONE CUDA graph per GPU per step
+  (forward, loss, backward, fused reduce+update, weight re-pack), which removes the GIL-bound
+  thread-per-GPU structure that makes the reference's DataParallel its worst scaler.
+"""
+from __future__ import annotations
+
+import copy
+
+import torch
+import torch.nn as nn
+
+from .. import _native as nv
+from ..ops import functional as fn
+from ..ops.modules import OutputLayout, pack_weights, packed_layers
+from .arena import BufferArena, ParamArena
+from .peer import PeerComm
+
+
+class _GatherLogits(torch.autograd.Function):
+    """[n_g,1,1,Cp] bf16 on GPU g  ->  rows of one [N,C] fp32 tensor on GPU 0.
+
+    Forward: every replica's conversion kernel stores into GPU 0's buffer (peer write).
+    Backward: every replica's conversion kernel loads its rows of dlogits from GPU 0 (peer read)
+    and leaves the bf16 gradient on its own GPU, so replica backwards run on their own devices.
+    """
+
+    @staticmethod
+    def forward(ctx, C, out_device, *xs):
+        N = sum(x.shape[0] for x in xs)
+        out = torch.empty((N, C), dtype=torch.float32, device=out_device)
+        main = torch.cuda.current_stream(out_device)
+        row, meta = 0, []
+        for x in xs:
+            n, Cp = x.shape[0], x.shape[-1]
+            with torch.cuda.device(x.device):
+                st = torch.cuda.current_stream(x.device)
+                nv.call("bf16_to_f32_unpad", nv.ptr(x), out[row: row + n].data_ptr(), n, C, Cp, st.cuda_stream)
+                ev = torch.cuda.Event()
+                ev.record(st)
+            main.wait_event(ev)
+            meta.append((x.device, row, n, Cp))
+            row += n
+        ctx.meta, ctx.C = meta, C
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        dy = dy.contiguous()
+        ev0 = torch.cuda.Event()
+        ev0.record(torch.cuda.current_stream(dy.device))
+        grads = []
+        for dev, row, n, Cp in ctx.meta:
+            with torch.cuda.device(dev):
+                st = torch.cuda.current_stream(dev)
+                st.wait_event(ev0)
+                dx = torch.empty((n, 1, 1, Cp), dtype=torch.bfloat16, device=dev)
+                nv.call("f32_to_bf16_pad", dy[row: row + n].data_ptr(), nv.ptr(dx), n, ctx.C, Cp, st.cuda_stream)
+            grads.append(dx)
+        return (None, None) + tuple(grads)
+
+
+class _ShardLoss(torch.autograd.Function):
+    """Softmax cross entropy of one replica's shard of a global batch of ``total`` samples.
+
+    The kernel adds this shard's share of the mean loss and its correct-prediction count into
+    ``stats`` -- a 2-float buffer that may live on another GPU -- and produces dlogits scaled by
+    1/total, so summing shard gradients over replicas gives the global-batch gradient.
+    """
+
+    @staticmethod
+    def forward(ctx, logits, targets, stats, total):
+        logits = logits.contiguous()
+        n, C = logits.shape
+        dl = torch.empty_like(logits)
+        nv.call("softmax_ce", nv.ptr(logits), nv.ptr(targets), nv.ptr(stats), 0, nv.ptr(dl), n, C, C,
+                1.0 / total, 1.0 / total, nv.stream_ptr())
+        ctx.save_for_backward(dl)
+        return torch.zeros((), device=logits.device)
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        return dl, None, None, None
+
+
+class DataParallel(nn.Module):
+    """``model = DataParallel(model)`` then use it like ``nn.DataParallel(model)``."""
+
+    def __init__(self, module, device_ids=None, bucket_cap_mb=25.0, first_bucket_mb=1.0):
+        super().__init__()
+        if not torch.cuda.is_available():
+            raise RuntimeError("DataParallel needs CUDA devices; use wrap() with backend='gloo' on CPU")
+        ids = list(range(torch.cuda.device_count())) if device_ids is None else list(device_ids)
+        self.devices = [torch.device("cuda", i) for i in ids]
+        self.world = len(self.devices)
+        self.module = module.to(self.devices[0])
+        # replicas live in a plain list: only replica 0 is a registered sub-module, so
+        # parameters() / state_dict() describe ONE model, with the "module." prefix
+        self.replicas = [self.module] + [copy.deepcopy(self.module).to(d) for d in self.devices[1:]]
+        self.comms = PeerComm.create_local(self.devices)
+        self.arenas, self.buffer_arenas, self.packed = [], [], []
+        for rep, dev in zip(self.replicas, self.devices):
+            with torch.cuda.device(dev):
+                self.arenas.append(ParamArena(rep.parameters(), dev, peer=None, bucket_cap_mb=bucket_cap_mb,
+                                              first_bucket_mb=first_bucket_mb))
+                self.buffer_arenas.append(BufferArena(list(rep.buffers()), dev, peer=None))
+                self.packed.append(packed_layers(rep))
+        numel = self.arenas[0].numel
+        pbufs = PeerComm.alloc_local(self.comms, numel * 4)
+        gbufs = PeerComm.alloc_local(self.comms, numel * 4)
+        bbufs = PeerComm.alloc_local(self.comms, self.buffer_arenas[0].nbytes)
+        for g, dev in enumerate(self.devices):
+            with torch.cuda.device(dev):
+                self.arenas[g].peer = self.comms[g]
+                self.arenas[g].adopt_symmetric(pbufs[g], gbufs[g])
+                self.buffer_arenas[g].adopt_symmetric(bbufs[g])
+            self.arenas[g].reducer = self      # lets FusedSGD(model.parameters()) find this engine
+        self.optimizer = None
+        self.state_sharded = False
+        outs = [m for m in self.module.modules() if isinstance(m, OutputLayout)]
+        if not outs:
+            raise RuntimeError("DataParallel needs a model built on this package's op layer "
+                               "(it must end in ops.OutputLayout)")
+        self.out_features = outs[-1].features
+        for d in self.devices:
+            torch.cuda.synchronize(d)
+
+    # ------------------------------------------------------------------ helpers
+    @property
+    def arena(self):
+        return self.arenas[0]
+
+    def shard_bounds(self, N):
+        per = (N + self.world - 1) // self.world
+        return [(g * per, min(N, (g + 1) * per)) for g in range(self.world)]
+
+    def sync_buffers_on(self, g):
+        """Replica 0's BatchNorm running statistics become replica g's (K-C2)."""
+        if self.world > 1 and self.buffer_arenas[0].nbytes > 16:
+            self.comms[g].broadcast(self.buffer_arenas[g].buf, 0, self.buffer_arenas[g].nbytes, root=0,
+                                    max_blocks=4)
+
+    def run_replica_body(self, g, x_slice):
+        """Replica g up to (not including) its OutputLayout; ``x_slice`` may be peer memory."""
+        rep = self.replicas[g]
+        last = [m for m in rep.modules() if isinstance(m, OutputLayout)][-1]
+        last._bypass = True
+        try:
+            return rep(x_slice)
+        finally:
+            last._bypass = False
+
+    def reduce_on(self, g, fused=True):
+        """Replica g's launches of the bucket collectives (same bucket order on every GPU)."""
+        opt, a, pc = self.optimizer, self.arenas[g], self.comms[g]
+        if self.world == 1:
+            if fused:
+                opt._local_update_on(g)
+            return
+        for bucket in a.buckets:
+            off_b, n = bucket.offset * 4, bucket.numel
+            two = pc.choose_two_shot(n * 4)
+            self.state_sharded = self.state_sharded or bool(two)
+            if fused:
+                m, v = opt._state_on(g)
+                pc.reduce_update(a.grad_buf, a.param_buf, m, v, opt._hyper_on(g), off_b, n, opt.opt_code,
+                                 two_shot=two, max_blocks=64)
+            else:
+                pc.allreduce(a.grad_buf, off_b, n, scale=1.0 / self.world, max_blocks=64)
+
+    # ------------------------------------------------------------------ nn.DataParallel contract
+    def forward(self, x):
+        """Input on GPU 0 (anything else is copied there), logits on GPU 0, autograd through all GPUs."""
+        d0 = self.devices[0]
+        if x.device != d0:
+            x = x.to(d0, non_blocking=True)
+        train = self.training and torch.is_grad_enabled()
+        if train and self.optimizer is not None:
+            self.optimizer.refresh_hyper()
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(d0))
+        outs = []
+        for g, (lo, hi) in enumerate(self.shard_bounds(x.shape[0])):
+            if lo >= hi:
+                continue
+            with torch.cuda.device(self.devices[g]):
+                torch.cuda.current_stream(self.devices[g]).wait_event(ev)
+                if train:
+                    self.sync_buffers_on(g)
+                outs.append(self.run_replica_body(g, x[lo:hi]))
+        return _GatherLogits.apply(self.out_features, d0, *outs)
+
+    # ------------------------------------------------------------------ reducer interface (FusedSGD)
+    def finish_step(self, fused=True):
+        """Called by ``optimizer.step()`` after backward: fused all-reduce+update per bucket per GPU."""
+        for g, dev in enumerate(self.devices):
+            with torch.cuda.device(dev):
+                self.reduce_on(g, fused)
+
+    def wait_gradients(self):
+        """For stock torch optimizers: averages gradients over replicas (call before step())."""
+        self.finish_step(fused=False)
+
+    def repack_all(self, caches):
+        for g, dev in enumerate(self.devices):
+            with torch.cuda.device(dev):
+                if self.packed[g]:
+                    pack_weights(self.packed[g], caches[g])
+
+    def train(self, mode=True):
+        super().train(mode)
+        for rep in self.replicas[1:]:
+            rep.train(mode)
+        return self
+
+    def close(self):
+        for pc in self.comms:
+            pc.close()
+
+
+class DataParallelStep:
+    """One training step over all replicas: ``loss = step(x, y)`` (x, y on CPU pinned or GPU 0).
+
+    After ``warmup`` eager iterations the per-replica work -- BN-stat sync, forward (first kernel
+    reads its shard of the input from GPU 0), loss (adds its share into GPU 0's loss buffer),
+    backward, fused bucket all-reduce + optimizer update, weight re-pack -- is captured into one
+    CUDA graph per GPU and replayed.  Returns a device tensor ``[mean loss, #correct]`` on GPU 0.
+    """
+
+    def __init__(self, model: DataParallel, optimizer, graph=True, warmup=2):
+        self.model, self.opt = model, optimizer
+        self.use_graph, self.warmup = graph, warmup
+        self.d0 = model.devices[0]
+        self._sx = self._st = None
+        self._graphs = None
+        self._calls = 0
+        self._stats = torch.zeros(2, device=self.d0)
+        self._streams = [torch.cuda.Stream(d) for d in model.devices]
+        self._done = None
+        self.launches_per_step = None
+
+    def _replica_step(self, g):
+        m, opt = self.model, self.opt
+        lo, hi = m.shard_bounds(self._sx.shape[0])[g]
+        if lo >= hi:
+            return
+        opt._hyper_devs[g].copy_(opt._hyper_host, non_blocking=True)
+        m.sync_buffers_on(g)
+        out = m.run_replica_body(g, self._sx[lo:hi])
+        logits = fn.to_f32(out, m.out_features)
+        loss = _ShardLoss.apply(logits, self._st[lo:hi], self._stats, self._sx.shape[0])
+        for p in m.arenas[g].params:
+            p._dtdl_fresh = True
+        loss.backward()
+        m.reduce_on(g, fused=True)
+        if m.packed[g]:
+            pack_weights(m.packed[g], opt._pack_caches[g])
+
+    def _run_all(self, capture=False):
+        m = self.model
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.d0))
+        graphs = []
+        for g, dev in enumerate(m.devices):
+            with torch.cuda.device(dev):
+                st = self._streams[g]
+                st.wait_event(ev)
+                if capture:
+                    gr = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(gr, stream=st, capture_error_mode="thread_local"):
+                        self._replica_step(g)
+                    graphs.append(gr)
+                elif self._graphs is not None:
+                    with torch.cuda.stream(st):
+                        self._graphs[g].replay()
+                else:
+                    with torch.cuda.stream(st):
+                        self._replica_step(g)
+        return graphs
+
+    def _join(self):
+        main = torch.cuda.current_stream(self.d0)
+        for g, dev in enumerate(self.model.devices):
+            ev = torch.cuda.Event()
+            with torch.cuda.device(dev):
+                ev.record(self._streams[g])
+            main.wait_event(ev)
+
+    def __call__(self, x, t):
+        m, opt = self.model, self.opt
+        with torch.cuda.device(self.d0):
+            if self._sx is None or self._sx.shape != x.shape:
+                self._sx = torch.empty(x.shape, dtype=torch.float32, device=self.d0)
+                self._st = torch.empty(t.shape, dtype=torch.int64, device=self.d0)
+                self._graphs, self._calls = None, 0
+            if opt.hyper_changes_every_step and self._done is not None:
+                self._done.synchronize()
+            opt.refresh_hyper(enqueue_copy=False)
+            self._sx.copy_(x, non_blocking=True)
+            self._st.copy_(t, non_blocking=True)
+            self._stats.zero_()
+        if self.use_graph and self._graphs is None and self._calls >= self.warmup:
+            for d in m.devices:
+                torch.cuda.synchronize(d)
+            nv.reset_launch_count()
+            graphs = self._run_all(capture=True)
+            self.launches_per_step = nv.launch_count()
+            self._graphs = graphs
+        self._calls += 1
+        self._run_all()
+        self._join()
+        opt._step += 1
+        if opt.hyper_changes_every_step:
+            self._done = torch.cuda.Event()
+            self._done.record(torch.cuda.current_stream(self.d0))
+        with torch.cuda.device(self.d0):
+            return self._stats.clone()

@@ -150,3 +150,55 @@ def ddp_training(i, world, outdir, use_graph):
         assert err < 5e-3, (n_, err)
     _ok(outdir, i)
     dtdl.shutdown()
+
+
+def data_parallel_engine(outdir):
+    """Single process driving all visible GPUs (nn.DataParallel contract + graph fast path)."""
+    import distributed_training_dl_b200 as dtdl
+    from distributed_training_dl_b200.models import PyramidNet
+    ndev = torch.cuda.device_count()
+    torch.manual_seed(0)
+    base = PyramidNet(num_layers=3, alpha=45.0)
+    single = copy.deepcopy(base).cuda(0)
+    dp = dtdl.DataParallel(base, device_ids=list(range(ndev)))
+    assert list(dp.state_dict().keys()) == ["module." + k for k in single.state_dict().keys()]
+    x = torch.randn(8 * ndev, 3, 32, 32, device="cuda:0")
+    t = torch.randint(0, 10, (8 * ndev,), device="cuda:0")
+    # inference contract: logits on GPU 0, equal to the single-GPU model (eval-mode BN)
+    dp.eval()
+    single.eval()
+    with torch.no_grad():
+        a, b = dp(x), single(x)
+    assert a.device == torch.device("cuda", 0) and a.shape == b.shape
+    assert (a - b).abs().max().item() < 2e-2 * max(1.0, b.abs().max().item())
+    # eager training through the DataParallel call contract
+    dp.train()
+    opt = dtdl.FusedSGD(dp.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+    for _ in range(2):
+        loss = F.cross_entropy(dp(x), t)
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+    for d in range(ndev):
+        torch.cuda.synchronize(d)
+    assert loss.item() == loss.item()
+
+    def replicas_identical():
+        ref = dp.arenas[0].param_flat
+        return all(torch.equal(ref.cpu(), a.param_flat.cpu()) for a in dp.arenas[1:])
+
+    assert replicas_identical(), "replicas diverged (eager)"
+    # graph fast path
+    step = dtdl.DataParallelStep(dp, opt, graph=True, warmup=2)
+    xs, ts = x.cpu().pin_memory(), t.cpu().pin_memory()
+    vals = []
+    for _ in range(6):
+        vals.append(step(xs, ts).cpu())
+    for d in range(ndev):
+        torch.cuda.synchronize(d)
+    assert all(v[0] == v[0] for v in vals), vals
+    assert vals[-1][0] < vals[0][0], [float(v[0]) for v in vals]   # same batch: loss goes down
+    assert replicas_identical(), "replicas diverged (graph)"
+    sd = opt.state_dict()
+    assert "momentum_buffer" in sd["state"][0]
+    open(os.path.join(outdir, "ok_dp"), "w").write("ok")

@@ -29,3 +29,13 @@ def test_ddp_training(tmp_path, use_graph):
     world = _world()
     dtdl.spawn(ddp_training, nprocs=world, args=(world, str(tmp_path), use_graph))
     assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
+
+
+def test_data_parallel_engine(tmp_path):
+    _world()
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    code = f"import sys; sys.path.insert(0, {here!r}); import _gpu_workers as w; w.data_parallel_engine({str(tmp_path)!r})"
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0 and os.path.exists(tmp_path / "ok_dp"), res.stdout[-2000:] + res.stderr[-4000:]
