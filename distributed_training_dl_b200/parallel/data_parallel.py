@@ -83,11 +83,13 @@ class _ShardLoss(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, logits, targets, stats, total):
+    def forward(ctx, logits, targets_ptr, stats_ptr, total):
+        # targets / stats are raw device pointers (GPU 0 memory): handing GPU-0 tensors to
+        # autograd would make the engine synchronise GPU 0's streams with this replica's
         logits = logits.contiguous()
         n, C = logits.shape
         dl = torch.empty_like(logits)
-        nv.call("softmax_ce", nv.ptr(logits), nv.ptr(targets), nv.ptr(stats), 0, nv.ptr(dl), n, C, C,
+        nv.call("softmax_ce", nv.ptr(logits), targets_ptr, stats_ptr, 0, nv.ptr(dl), n, C, C,
                 1.0 / total, 1.0 / total, nv.stream_ptr())
         ctx.save_for_backward(dl)
         return torch.zeros((), device=logits.device)
@@ -194,14 +196,19 @@ class DataParallel(nn.Module):
             self.optimizer.refresh_hyper()
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream(d0))
+        # Kernels that wait for another GPU are launched for ALL GPUs back to back, with
+        # nothing in between that could block the host (an allocation, a synchronous copy):
+        # a GPU spinning on a peer whose kernel the host has not launched yet would deadlock.
+        for g, dev in enumerate(self.devices):
+            with torch.cuda.device(dev):
+                torch.cuda.current_stream(dev).wait_event(ev)
+                if train:
+                    self.sync_buffers_on(g)
         outs = []
         for g, (lo, hi) in enumerate(self.shard_bounds(x.shape[0])):
             if lo >= hi:
                 continue
             with torch.cuda.device(self.devices[g]):
-                torch.cuda.current_stream(self.devices[g]).wait_event(ev)
-                if train:
-                    self.sync_buffers_on(g)
                 outs.append(self.run_replica_body(g, x[lo:hi]))
         return _GatherLogits.apply(self.out_features, d0, *outs)
 
@@ -240,6 +247,10 @@ class DataParallelStep:
     reads its shard of the input from GPU 0), loss (adds its share into GPU 0's loss buffer),
     backward, fused bucket all-reduce + optimizer update, weight re-pack -- is captured into one
     CUDA graph per GPU and replayed.  Returns a device tensor ``[mean loss, #correct]`` on GPU 0.
+
+    Known limitation: an autograd graph built through ``DataParallel.forward`` (the eager call
+    contract) must not be alive when the capture happens -- drop such a ``loss`` first; CUDA
+    otherwise reports a dependency of the captured stream on uncaptured work.
     """
 
     def __init__(self, model: DataParallel, optimizer, graph=True, warmup=2):
@@ -254,22 +265,32 @@ class DataParallelStep:
         self._done = None
         self.launches_per_step = None
 
-    def _replica_step(self, g):
+    def _replica_step(self, g, phase=None):
+        """Replica g's whole step (``phase=None``, used under graph capture where nothing runs
+        on the host side), or one phase of it: eager execution keeps the cross-GPU kernels of
+        all replicas (phases 0 and 2) free of interleaved host work that might block."""
         m, opt = self.model, self.opt
         lo, hi = m.shard_bounds(self._sx.shape[0])[g]
         if lo >= hi:
             return
+        if phase in (None, 0):
+            m.sync_buffers_on(g)
+        if phase in (None, 1):
+            self._fwd_bwd(g, lo, hi)
+        if phase in (None, 2):
+            m.reduce_on(g, fused=True)
+        if phase in (None, 3) and m.packed[g]:
+            pack_weights(m.packed[g], opt._pack_caches[g])
+
+    def _fwd_bwd(self, g, lo, hi):
+        m, opt = self.model, self.opt
         opt._hyper_devs[g].copy_(opt._hyper_host, non_blocking=True)
-        m.sync_buffers_on(g)
         out = m.run_replica_body(g, self._sx[lo:hi])
         logits = fn.to_f32(out, m.out_features)
-        loss = _ShardLoss.apply(logits, self._st[lo:hi], self._stats, self._sx.shape[0])
+        loss = _ShardLoss.apply(logits, self._st[lo:hi].data_ptr(), self._stats.data_ptr(), self._sx.shape[0])
         for p in m.arenas[g].params:
             p._dtdl_fresh = True
         loss.backward()
-        m.reduce_on(g, fused=True)
-        if m.packed[g]:
-            pack_weights(m.packed[g], opt._pack_caches[g])
 
     def _run_all(self, capture=False):
         m = self.model
@@ -288,9 +309,11 @@ class DataParallelStep:
                 elif self._graphs is not None:
                     with torch.cuda.stream(st):
                         self._graphs[g].replay()
-                else:
-                    with torch.cuda.stream(st):
-                        self._replica_step(g)
+        if not capture and self._graphs is None:
+            for phase in range(4):
+                for g, dev in enumerate(m.devices):
+                    with torch.cuda.device(dev), torch.cuda.stream(self._streams[g]):
+                        self._replica_step(g, phase)
         return graphs
 
     def _join(self):

@@ -188,6 +188,7 @@ def data_parallel_engine(outdir):
         return all(torch.equal(ref.cpu(), a.param_flat.cpu()) for a in dp.arenas[1:])
 
     assert replicas_identical(), "replicas diverged (eager)"
+    del loss  # an autograd graph of the eager path must not be alive while graphs are captured
     # graph fast path
     step = dtdl.DataParallelStep(dp, opt, graph=True, warmup=2)
     xs, ts = x.cpu().pin_memory(), t.cpu().pin_memory()
