@@ -29,8 +29,9 @@ class CrossEntropyLoss(nn.Module):
 
     def forward(self, logits, targets):
         if not logits.is_cuda:
-            self.last_stats = None
-            return F.cross_entropy(logits, targets)
+            loss = F.cross_entropy(logits, targets)
+            self.last_stats = torch.stack([loss.detach(), (logits.detach().argmax(1) == targets).sum().float()])
+            return loss
         loss, stats = fn.softmax_cross_entropy(logits, targets)
         self.last_stats = stats
         return loss
@@ -52,10 +53,9 @@ class TrainStep:
         self.device = next(model.parameters()).device
         self.use_graph = graph and self.device.type == "cuda"
         self.warmup = warmup
-        self._graph = None
-        self._calls = 0
+        self._slots = {}
         self._done = None
-        self._sx = self._st = self._loss = self._stats = None
+        self._stats = None
         self.launches_per_step = None
 
     # ------------------------------------------------------------------
@@ -67,26 +67,31 @@ class TrainStep:
         self.optimizer.step()
         return loss, getattr(self.criterion, "last_stats", None)
 
-    def _stage(self, x, t):
-        if self._sx is None or self._sx.shape != x.shape or self._st.shape != t.shape:
-            self._sx = torch.empty(x.shape, dtype=x.dtype, device=self.device)
-            self._st = torch.empty(t.shape, dtype=t.dtype, device=self.device)
-            self._graph = None
-            self._calls = 0
-        self._sx.copy_(x, non_blocking=True)
-        self._st.copy_(t, non_blocking=True)
+    def _slot(self, x, t):
+        """Static buffers + graph per batch shape (a smaller last batch gets its own slot and
+        simply stays eager until it has been seen ``warmup`` times)."""
+        key = (tuple(x.shape), tuple(t.shape))
+        slot = self._slots.get(key)
+        if slot is None:
+            slot = {"sx": torch.empty(x.shape, dtype=x.dtype, device=self.device),
+                    "st": torch.empty(t.shape, dtype=t.dtype, device=self.device),
+                    "graph": None, "calls": 0, "loss": None, "stats": None}
+            self._slots[key] = slot
+        slot["sx"].copy_(x, non_blocking=True)
+        slot["st"].copy_(t, non_blocking=True)
+        return slot
 
-    def _capture(self):
+    def _capture(self, slot):
         opt = self.optimizer
         nv.reset_launch_count()
         g = torch.cuda.CUDAGraph()
         step_before = getattr(opt, "_step", None)
         with torch.cuda.graph(g):
-            loss, stats = self._eager(self._sx, self._st)
+            loss, stats = self._eager(slot["sx"], slot["st"])
         if step_before is not None:
             opt._step = step_before  # capture does not execute; replays advance the counter
         self.launches_per_step = nv.launch_count()
-        self._graph, self._loss, self._stats = g, loss, stats
+        slot.update(graph=g, loss=loss, stats=stats)
 
     def __call__(self, x, t):
         if not self.use_graph:
@@ -94,26 +99,27 @@ class TrainStep:
                 x, t = x.to(self.device, non_blocking=True), t.to(self.device, non_blocking=True)
             loss, self._stats = self._eager(x, t)
             return loss
-        self._stage(x, t)
-        if self._graph is None:
-            if self._calls < self.warmup:
-                self._calls += 1
-                loss, self._stats = self._eager(self._sx, self._st)
+        slot = self._slot(x, t)
+        if slot["graph"] is None:
+            if slot["calls"] < self.warmup:
+                slot["calls"] += 1
+                loss, self._stats = self._eager(slot["sx"], slot["st"])
                 return loss
             torch.cuda.synchronize(self.device)
-            self._capture()
+            self._capture(slot)
         opt = self.optimizer
         if hasattr(opt, "refresh_hyper"):
             if getattr(opt, "hyper_changes_every_step", False) and self._done is not None:
                 self._done.synchronize()  # the previous replay must have read its values
             opt.refresh_hyper(enqueue_copy=False)  # the graph re-reads the pinned block
-        self._graph.replay()
+        slot["graph"].replay()
         if getattr(opt, "hyper_changes_every_step", False):
             self._done = torch.cuda.Event()
             self._done.record()
         if hasattr(opt, "_step"):
             opt._step += 1
-        return self._loss
+        self._stats = slot["stats"]
+        return slot["loss"]
 
     @property
     def last_stats(self):
