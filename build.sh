@@ -7,7 +7,7 @@ mkdir -p "$OUT" build
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS=(-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC
        -Xptxas -v --expt-relaxed-constexpr -Iinclude)
-SRCS=(csrc/common/host.cpp csrc/common/api.cpp csrc/ops/conv_gemm.cu csrc/ops/conv_wgrad.cu
+SRCS=(csrc/common/host.cpp csrc/common/api.cpp csrc/ops/conv_gemm.cu csrc/ops/conv_gemm_v2.cu csrc/ops/conv_wgrad.cu
       csrc/ops/nn_ops.cu csrc/ops/pack.cu csrc/comm/collectives.cu)
 OBJS=()
 pids=()

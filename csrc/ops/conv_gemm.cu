@@ -26,6 +26,8 @@
 #include "../common/ptx.cuh"
 #include "../../include/dtdl_b200.h"
 
+#include <stdlib.h>
+
 namespace dtdl {
 
 struct ConvGemmArgs {
@@ -217,6 +219,10 @@ void choose_pixel_tile(int N, int Ho, int Wo, int* BW, int* BH, int* BNi) {
   *BNi = bn;
 }
 
+int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, int N, int H, int W,
+                  int Cin_p, int Ho, int Wo, int Cout_p, int KH, int KW, int pad_h, int pad_w,
+                  int flags, cudaStream_t stream);
+
 }  // namespace dtdl
 
 using namespace dtdl;
@@ -226,8 +232,16 @@ extern "C" int dtdl_conv_fprop(const void* x, const void* wpack, void* y, const 
                                int pad_h, int pad_w, int flags, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTDL_REQUIRE(Cin_p % 8 == 0 && Cout_p % 8 == 0, "channel counts must be padded to 8");
-  DTDL_REQUIRE(Ho == H + 2 * pad_h - KH + 1 && Wo == W + 2 * pad_w - KW + 1,
+  // Ho / Wo may be smaller than the full stride-1 output (asymmetric padding: the caller
+  // simply asks for fewer rows / columns on the high side).
+  DTDL_REQUIRE(Ho >= 1 && Wo >= 1 && Ho <= H + 2 * pad_h - KH + 1 && Wo <= W + 2 * pad_w - KW + 1,
                "output size does not match a stride-1 convolution");
+  static const bool force_v1 = getenv("DTDL_CONV_V1") != nullptr;
+  if (!force_v1) {
+    const int rc = conv_fprop_v2(x, wpack, y, bias, N, H, W, Cin_p, Ho, Wo, Cout_p, KH, KW, pad_h,
+                                 pad_w, flags, stream);
+    if (rc >= 0) return rc;  // launched (0) or failed (>0); -1 = shape not covered, fall through
+  }
   ConvGemmArgs a;
   a.taps = KH * KW;
   a.KW = KW;
