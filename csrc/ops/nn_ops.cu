@@ -73,6 +73,36 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, uint4* __restri
   }
 }
 
+// NCHW fp32 -> 2x2 space-to-depth NHWC bf16: y[n, ho, wo, (bh*2+bw)*C + c] = x[n, c, 2ho+bh, 2wo+bw].
+// Turns a stride-2 KxK convolution into a stride-1 ceil(K/2) x ceil(K/2) one over 4C channels
+// (ResNet's 7x7/2 stem becomes 4x4/1 over 12 channels).
+__global__ void nchw_to_s2d_kernel(const float* __restrict__ x, uint4* __restrict__ y, int N, int C,
+                                   int H, int W, int G) {
+  const int Ho = H / 2, Wo = W / 2;
+  const long long total = (long long)N * Ho * Wo * G;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int g = (int)(i % G);
+    long long t = i / G;
+    const int wo = (int)(t % Wo);
+    t /= Wo;
+    const int ho = (int)(t % Ho);
+    const long long n = t / Ho;
+    F8 f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int ch = g * 8 + k;
+      float v = 0.f;
+      if (ch < 4 * C) {
+        const int phase = ch / C, c = ch % C;
+        v = x[((n * C + c) * H + 2 * ho + (phase >> 1)) * W + 2 * wo + (phase & 1)];
+      }
+      f.v[k] = v;
+    }
+    y[i] = pack8(f);
+  }
+}
+
 // ---------------------------------------------------------------------------
 // Per-channel sum / sum of squares (accumulated with atomics into sums[2*Cp]).
 // ---------------------------------------------------------------------------
@@ -661,6 +691,17 @@ extern "C" int dtdl_nchw_to_nhwc_bf16(const float* x, void* y, int N, int C, int
   const long long total = (long long)N * H * W * G;
   nchw_to_nhwc_kernel<<<grid_for(total, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
       x, reinterpret_cast<uint4*>(y), N, C, H * W, G);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_nchw_to_s2d_bf16(const float* x, void* y, int N, int C, int H, int W, int Cp,
+                                     void* stream) {
+  DTDL_REQUIRE(Cp % 8 == 0 && Cp >= 4 * C && H % 2 == 0 && W % 2 == 0, "bad space-to-depth shape");
+  const int G = Cp / 8;
+  const long long total = (long long)N * (H / 2) * (W / 2) * G;
+  nchw_to_s2d_kernel<<<grid_for(total, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
+      x, reinterpret_cast<uint4*>(y), N, C, H, W, G);
   DTDL_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -70,6 +70,8 @@ int dtdl_pack_weights(const void* device_table, int n_entries, long long total_b
  * softmax cross entropy + accuracy count (pytorch/single_gpu.py:99,105-108). */
 int dtdl_nchw_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, int Cp,
                            void* stream);
+int dtdl_nchw_to_s2d_bf16(const float* x, void* y, int N, int C, int H, int W, int Cp,
+                          void* stream);
 int dtdl_bn_stats(const void* x, float* sums /* [2*Cp], zeroed */, long long P, int Cp,
                   void* stream);
 int dtdl_bn_apply(const void* x, void* y, const float* sums, const float* gamma, const float* beta,

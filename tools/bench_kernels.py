@@ -29,7 +29,8 @@ def timeit(f, reps=20, flush=True):
 
 def main():
     N = 64
-    shapes = [(16, 21, 32), (56, 61, 32), (96, 101, 32), (141, 146, 16), (181, 186, 16), (226, 231, 8), (266, 271, 8)]
+    import os
+    shapes = eval(os.environ['SHAPES']) if 'SHAPES' in os.environ else [(16, 21, 32), (56, 61, 32), (96, 101, 32), (141, 146, 16), (181, 186, 16), (226, 231, 8), (266, 271, 8)]
     print(f"{'shape':>22s} {'fprop us':>9s} {'TF/s':>6s} {'dgrad us':>9s} {'wgrad us':>9s} {'TF/s':>6s} {'bn fwd':>7s} {'bn bwd':>7s} {'GB/s':>6s}")
     for cin, cout, hw in shapes:
         conv = Conv2d(cin, cout, 3, padding=1, bias=False).cuda()

@@ -1,0 +1,22 @@
+"""Small single-GPU program for ncu captures: a few launches of each hot kernel on one
+PyramidNet stage-1 shape (batch 64, 32x32, 56->61 channels)."""
+import sys
+import torch
+sys.path.insert(0, ".")
+from distributed_training_dl_b200 import _native as nv
+from distributed_training_dl_b200.ops import Conv2d, functional as fn
+
+cin, cout, hw, N = (int(v) for v in (sys.argv[1:5] if len(sys.argv) > 4 else (56, 61, 32, 64)))
+conv = Conv2d(cin, cout, 3, padding=1, bias=False).cuda()
+conv._ensure_packed()
+x = torch.randn(N, hw, hw, conv.Cin_p, device="cuda").bfloat16()
+dy = torch.randn(N, hw, hw, conv.Cout_p, device="cuda").bfloat16()
+gw = torch.zeros_like(conv.weight)
+need = nv.lib().dtdl_conv_wgrad_workspace_bytes(N, hw, hw, conv.Cin_p, conv.Cout_p, 3, 3)
+ws = fn.scratch(x.device, need)
+for _ in range(4):
+    y = fn.conv_fprop_raw(x, conv.wf, conv.Cout_p, 3, 3, 1)
+    nv.call("conv_wgrad", nv.ptr(x), nv.ptr(dy), nv.ptr(gw), nv.ptr(ws), ws.numel(), N, hw, hw, cin, conv.Cin_p,
+            hw, hw, cout, conv.Cout_p, 3, 3, 1, 1, 0, nv.stream_ptr())
+torch.cuda.synchronize()
+print("ok", float(y.float().abs().mean()))
