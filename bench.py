@@ -39,7 +39,7 @@ def parse():
     p.add_argument("--steps", type=int, default=50)
     p.add_argument("--warmup", type=int, default=5)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    p.add_argument("--model", default="pyramidnet", choices=["pyramidnet", "mnist_cnn", "mlp"])
+    p.add_argument("--model", default="pyramidnet", choices=["pyramidnet", "resnet50", "mnist_cnn", "mlp"])
     p.add_argument("--batch-size", type=int, default=PER_GPU_BATCH, help="per-GPU batch")
     p.add_argument("--no-graph", action="store_true", help="ours: eager launches instead of a CUDA graph")
     p.add_argument("--no-e2e", action="store_true")
@@ -55,10 +55,11 @@ def dist_env():
 
 def synthetic_batches(model, batch, n_sets, pin=True):
     import torch
-    shape = {"pyramidnet": (3, 32, 32), "mnist_cnn": (1, 28, 28), "mlp": (784,)}[model]
+    shape = {"pyramidnet": (3, 32, 32), "resnet50": (3, 224, 224), "mnist_cnn": (1, 28, 28), "mlp": (784,)}[model]
+    classes = 1000 if model == "resnet50" else 10
     g = torch.Generator().manual_seed(1234 + dist_env()[0])
     xs = [torch.randn((batch,) + shape, generator=g) for _ in range(n_sets)]
-    ts = [torch.randint(0, 10, (batch,), generator=g) for _ in range(n_sets)]
+    ts = [torch.randint(0, classes, (batch,), generator=g) for _ in range(n_sets)]
     if pin and torch.cuda.is_available():
         xs, ts = [x.pin_memory() for x in xs], [t.pin_memory() for t in ts]
     return xs, ts
@@ -93,11 +94,11 @@ def run_ours(args):
     rank, world, local = dist_env()
     comm = dtdl.init(backend="b200")  # env:// from torchrun, or single process
     dev = comm.device
-    make = {"pyramidnet": dtdl.models.pyramidnet, "mnist_cnn": dtdl.models.MnistCNN,
-            "mlp": dtdl.models.MLP}[args.model]
+    make = {"pyramidnet": dtdl.models.pyramidnet, "resnet50": dtdl.models.resnet50,
+            "mnist_cnn": dtdl.models.MnistCNN, "mlp": dtdl.models.MLP}[args.model]
     torch.manual_seed(0)
     net = dtdl.wrap(make().to(dev))
-    if args.model == "pyramidnet":
+    if args.model in ("pyramidnet", "resnet50"):
         opt = dtdl.FusedSGD(net.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
     else:
         opt = dtdl.FusedAdam(net.parameters(), keras=(args.model == "mnist_cnn"))
@@ -164,7 +165,7 @@ def load_reference_model():
 
 
 def run_reference(args):
-    if args.model != "pyramidnet":
+    if args.model not in ("pyramidnet", "resnet50"):
         print(json.dumps({"impl": "reference", "unavailable":
                           "TensorFlow 2 / Chainer are not installed on this image (BASELINE.md section 4)"}))
         return
@@ -189,7 +190,11 @@ def run_reference(args):
             os.environ.get("MASTER_ADDR", "127.0.0.1"), os.environ.get("MASTER_PORT", "29500")),
             world_size=world, rank=rank)
     torch.manual_seed(0)
-    net = mod.pyramidnet()
+    if args.model == "resnet50":   # not in the reference repo: torchvision's definition, bf16 autocast
+        import torchvision
+        net = torchvision.models.resnet50()
+    else:
+        net = mod.pyramidnet()
     net.cuda(local)
     if world > 1:
         net = torch.nn.parallel.DistributedDataParallel(net, device_ids=[local], output_device=local)
@@ -197,16 +202,18 @@ def run_reference(args):
     optimizer = optim.SGD(net.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
     net.train()
     B = args.batch_size
-    xs, ts = synthetic_batches("pyramidnet", B, 8)
+    xs, ts = synthetic_batches(args.model, B, 8)
     dxs, dts = [x.to(dev) for x in xs], [t.to(dev) for t in ts]
+    amp = args.model == "resnet50"
 
     def barrier():
         if world > 1:
             dist.barrier()
 
     def core(inputs, targets):
-        outputs = net(inputs)
-        loss = criterion(outputs, targets)
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=amp):
+            outputs = net(inputs)
+            loss = criterion(outputs, targets)
         optimizer.zero_grad()
         loss.backward()
         optimizer.step()
@@ -241,7 +248,7 @@ def run_reference(args):
                "h2d_bytes_per_step": world * (xs[0].numel() * 4 + ts[0].numel() * 8),
                "d2h_bytes_per_step": world * 12}
     res = result_line(args, "reference", world, value, ms, clocks, e2e, 0,
-                      dtype="fp32 (TF32 conv allowed: torch default)",
+                      dtype="bf16 autocast" if amp else "fp32 (TF32 conv allowed: torch default)",
                       extra={"parallelism": f"dp{world}", "comm": "NCCL" if world > 1 else "none",
                              "model_file": os.path.relpath(path, ROOT) if path.startswith(ROOT) else path})
     if rank == 0:
@@ -252,10 +259,11 @@ def run_reference(args):
 
 def result_line(args, impl, world, value, ms, clocks, e2e, launches, dtype, extra):
     cfg = {"model": {"pyramidnet": "PyramidNet-110 a270 (pytorch/model.py), CIFAR-shaped 3x32x32",
+                     "resnet50": "ResNet-50, ImageNet-shaped 3x224x224, 1000 classes",
                      "mnist_cnn": "Keras MNIST CNN (tensorflow2/mnist_single.py)",
                      "mlp": "Chainer MLP 784-1000-1000-10"}[args.model],
            "global_batch": world * args.batch_size, "per_gpu_batch": args.batch_size, "seq_len": None,
-           "optimizer": "SGD lr 0.1 momentum 0.9 wd 1e-4" if args.model == "pyramidnet" else "Adam",
+           "optimizer": "SGD lr 0.1 momentum 0.9 wd 1e-4" if args.model in ("pyramidnet", "resnet50") else "Adam",
            "l2": "256 MiB memset between steps, inside the timed region"}
     cfg.update(extra)
     out = {"metric": "images/sec (train step: fwd+loss+bwd+allreduce+SGD update), device-timed, max over ranks",

@@ -286,7 +286,7 @@ extern "C" int dtdl_conv_wgrad(const void* x, const void* dy, float* dw, void* w
                                int pad_w, int accumulate, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTDL_REQUIRE(Cin_p % 8 == 0 && Cout_p % 8 == 0, "channel counts must be padded to 8");
-  DTDL_REQUIRE(Ho == H + 2 * pad_h - KH + 1 && Wo == W + 2 * pad_w - KW + 1,
+  DTDL_REQUIRE(Ho >= 1 && Wo >= 1 && Ho <= H + 2 * pad_h - KH + 1 && Wo <= W + 2 * pad_w - KW + 1,
                "output size does not match a stride-1 convolution");
   WgradArgs a;
   int splits;

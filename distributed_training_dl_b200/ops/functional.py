@@ -144,9 +144,9 @@ def _conv_out(n, k, pad):
     return n + 2 * pad - k + 1
 
 
-def conv_fprop_raw(x, wpack, Cout_p, KH, KW, pad, bias=None, relu=False, out_f32=False):
+def conv_fprop_raw(x, wpack, Cout_p, KH, KW, pad, bias=None, relu=False, out_f32=False, out_hw=None):
     N, H, W, Cin_p = x.shape
-    Ho, Wo = _conv_out(H, KH, pad), _conv_out(W, KW, pad)
+    Ho, Wo = out_hw or (_conv_out(H, KH, pad), _conv_out(W, KW, pad))
     y = torch.empty((N, Ho, Wo, Cout_p), dtype=torch.float32 if out_f32 else torch.bfloat16,
                     device=x.device)
     flags = (1 if relu else 0) | (2 if out_f32 else 0)
@@ -179,7 +179,7 @@ class _Conv(torch.autograd.Function):
     def forward(ctx, x, weight, bias, mod):
         x = x.contiguous()
         y = conv_fprop_raw(x, mod.wf, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad, bias=bias,
-                           relu=mod.fuse_relu, out_f32=False)
+                           relu=mod.fuse_relu, out_f32=False, out_hw=getattr(mod, "out_hw", None))
         full_hw = (y.shape[1], y.shape[2])
         if mod.conv_stride == 2:
             y = subsample2_raw(y)
@@ -210,22 +210,59 @@ class _Conv(torch.autograd.Function):
             dy = subsample2_raw(dy, adjoint=True, full_hw=ctx.full_hw)
         N, H, W, Cin_p = x.shape
         Ho, Wo = ctx.full_hw
-        # weight gradient
-        gw, acc = grad_buffer(weight)
+        # weight gradient: straight into the parameter's gradient buffer, or -- when the weight
+        # is a computed tensor (ResNet stem's space-to-depth view) -- returned to autograd
+        returned = getattr(mod, "return_wgrad", False)
+        if returned:
+            gw, acc = torch.empty(weight.shape, dtype=torch.float32, device=weight.device), 0
+        else:
+            gw, acc = grad_buffer(weight)
         need = nv.lib().dtdl_conv_wgrad_workspace_bytes(N, Ho, Wo, Cin_p, mod.Cout_p, mod.KH, mod.KW)
         ws = scratch(x.device, need)
         nv.call("conv_wgrad", nv.ptr(x), nv.ptr(dy), nv.ptr(gw), nv.ptr(ws), ws.numel(), N, H, W,
                 mod.Cin, Cin_p, Ho, Wo, mod.Cout, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad, mod.conv_pad, acc, st)
-        _grad_ready(weight)
+        if not returned:
+            _grad_ready(weight)
         # data gradient
         dx = None
         if ctx.needs_input_grad[0]:
             dx = conv_fprop_raw(dy, mod.wd, Cin_p, mod.KH, mod.KW, mod.KH - 1 - mod.conv_pad)
-        return dx, None, None, None
+        return dx, (gw if returned else None), None, None
 
 
 def conv(x, mod):
     return _Conv.apply(x, mod.weight, mod.bias, mod)
+
+
+class _Subsample(torch.autograd.Function):
+    """y[n,ho,wo] = x[n,2ho,2wo]: a stride-2 1x1 convolution is this followed by a stride-1 one."""
+
+    @staticmethod
+    def forward(ctx, x):
+        x = x.contiguous()
+        ctx.full_hw = (x.shape[1], x.shape[2])
+        return subsample2_raw(x)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return subsample2_raw(dy.contiguous(), adjoint=True, full_hw=ctx.full_hw)
+
+
+def subsample2(x):
+    return _Subsample.apply(x)
+
+
+def to_s2d(x: torch.Tensor) -> torch.Tensor:
+    """NCHW fp32 -> 2x2 space-to-depth NHWC bf16 [N,H/2,W/2,pad8(4C)] (ResNet stem input)."""
+    N, C, H, W = x.shape
+    Cp = pad8(4 * C)
+    x = x.detach()
+    if x.dtype != torch.float32 or not x.is_contiguous():
+        x = x.contiguous().float()
+    y = torch.empty((N, H // 2, W // 2, Cp), dtype=torch.bfloat16,
+                    device=torch.device("cuda", torch.cuda.current_device()))
+    nv.call("nchw_to_s2d_bf16", nv.ptr(x), nv.ptr(y), N, C, H, W, Cp, nv.stream_ptr())
+    return y
 
 
 # --------------------------------------------------------------------------------------

@@ -99,8 +99,10 @@ class Conv2d(nn.Conv2d, _PackedWeightMixin):
         assert k[0] == k[1] and self.padding[0] == self.padding[1], "square kernels only"
         assert self.stride[0] == self.stride[1] and self.stride[0] in (1, 2), "stride 1 or 2"
         assert self.dilation == (1, 1) and self.groups == 1
-        self._init_pack_meta(out_channels, in_channels, k[0], k[1], self.padding[0], self.stride[0],
-                             need_dgrad=not first_layer)
+        # a stride-2 1x1 convolution only ever looks at every other pixel: sub-sample first
+        self.pre_subsample = k[0] == 1 and self.stride[0] == 2
+        self._init_pack_meta(out_channels, in_channels, k[0], k[1], self.padding[0],
+                             1 if self.pre_subsample else self.stride[0], need_dgrad=not first_layer)
         self.fuse_relu = activation == "relu"
         assert activation in (None, "relu")
 
@@ -109,6 +111,8 @@ class Conv2d(nn.Conv2d, _PackedWeightMixin):
             y = super().forward(x)
             return F.relu(y) if self.fuse_relu else y
         self._ensure_packed()
+        if self.pre_subsample:
+            x = fn.subsample2(x)
         return fn.conv(x, self)
 
 

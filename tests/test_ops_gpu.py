@@ -35,6 +35,9 @@ CONV_CASES = [
     (4, 64, 64, 5, 5, 3, 0, 1),
     (2, 64, 256, 14, 14, 1, 0, 1),
     (3, 300, 520, 7, 7, 1, 0, 1),
+    (2, 64, 128, 14, 14, 1, 0, 2),      # stride-2 1x1 shortcut (sub-sample first)
+    (2, 128, 128, 28, 28, 3, 1, 2),     # ResNet stride-2 3x3
+    (2, 64, 64, 56, 56, 3, 1, 1),       # 56-wide rows: 112-row tiles
 ]
 
 
@@ -199,3 +202,45 @@ def test_models_match_cpu_oracle():
             cos = torch.dot(ga, gb) / (ga.norm() * gb.norm() + 1e-30)
             assert cos > min_cos, (n, cos.item())
             assert 0.7 < (gb.norm() / ga.norm()).item() < 1.4, n
+
+
+def test_resnet_stem_space_to_depth():
+    """7x7/2 stem computed as 4x4/1 over the space-to-depth image == F.conv2d(stride 2, pad 3)."""
+    from distributed_training_dl_b200.models import StemConv7x7s2
+    torch.manual_seed(0)
+    stem = StemConv7x7s2().cuda()
+    with torch.no_grad():
+        stem.weight.copy_(_bf(stem.weight))
+    x = _bf(torch.randn(2, 3, 64, 64, device="cuda"))
+    y = stem(x)
+    rw = stem.weight.detach().clone().requires_grad_(True)
+    ry = F.conv2d(x, rw, stride=2, padding=3)
+    assert y.shape[1:3] == ry.shape[2:]
+    assert _rel_err(_nhwc_to_nchw(y, 64), ry) < 1e-2
+    dy = _bf(torch.randn_like(ry))
+    ry.backward(dy)
+    from distributed_training_dl_b200.ops import functional as fn
+    y.backward(fn.to_nhwc(dy))
+    assert _rel_err(stem.weight.grad, rw.grad) < 1e-2
+
+
+def test_resnet50_matches_cpu_oracle():
+    import copy
+    from distributed_training_dl_b200.models import resnet50
+    torch.manual_seed(0)
+    cpu = resnet50(num_classes=100)
+    gpu = copy.deepcopy(cpu).cuda()
+    x = torch.randn(4, 3, 64, 64)
+    t = torch.randint(0, 100, (4,))
+    lc = F.cross_entropy(cpu(x), t)
+    lg = F.cross_entropy(gpu(x.cuda()), t.cuda())
+    assert abs(lc.item() - lg.item()) < 0.1 * max(1.0, abs(lc.item())), (lc.item(), lg.item())
+    lc.backward()
+    lg.backward()
+    for (n, a), (_, b) in zip(cpu.named_parameters(), gpu.named_parameters()):
+        assert b.grad is not None, n
+        ga, gb = a.grad.flatten().double(), b.grad.cpu().flatten().double()
+        if ga.norm() < 1e-5:
+            continue
+        cos = torch.dot(ga, gb) / (ga.norm() * gb.norm() + 1e-30)
+        assert cos > 0.9, (n, cos.item())
