@@ -31,6 +31,8 @@ class _StemOperand(_PackedWeightMixin):
         self.weight = None
         self.return_wgrad = True      # the 4x4 kernel is a view of the 7x7 parameter: autograd maps it back
         self.out_hw = None
+        self.pack_src = None          # persistent fp32 copy the pack kernel reads (stable pointer)
+        self._table = {}
 
 
 class StemConv7x7s2(nn.Conv2d):
@@ -56,7 +58,12 @@ class StemConv7x7s2(nn.Conv2d):
         op = self._op
         op.weight = self.s2d_weight(self.weight)
         op.out_hw = (H // 2, W // 2)
-        op._ensure_packed()
+        if op.pack_src is None or op.pack_src.device != x.device:
+            op.pack_src = torch.empty(op.weight.shape, dtype=torch.float32, device=x.device)
+            op._alloc_packs(x.device)
+            op._table = {}
+        op.pack_src.copy_(op.weight.detach())
+        L.pack_weights([op], op._table)
         return fn.conv(fn.to_s2d(x), op)
 
 

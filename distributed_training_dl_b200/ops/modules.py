@@ -71,8 +71,9 @@ def pack_weights(modules, table_cache=None):
             if m.wf is None or m.wf.device != m.weight.device:
                 m._alloc_packs(m.weight.device)
             entry = ctypes.addressof(host) + i * esz
+            src = getattr(m, "pack_src", None)
             blocks += nv.lib().dtdl_pack_entry_fill(
-                entry, nv.ptr(m.weight), nv.ptr(m.wf), nv.ptr(m.wd), m.Cout, m.Cin, m.KH * m.KW,
+                entry, nv.ptr(src if src is not None else m.weight), nv.ptr(m.wf), nv.ptr(m.wd), m.Cout, m.Cin, m.KH * m.KW,
                 m.Cin_p, m.Cout_p, blocks)
         dev = modules[0].weight.device
         table = torch.frombuffer(bytearray(bytes(host)), dtype=torch.uint8).to(dev)

@@ -224,23 +224,59 @@ def test_resnet_stem_space_to_depth():
     assert _rel_err(stem.weight.grad, rw.grad) < 1e-2
 
 
-def test_resnet50_matches_cpu_oracle():
+def test_resnet_bottlenecks_match_cpu_oracle():
+    """Every kind of ResNet-50 block (with / without projection shortcut, stride 1 / 2, all
+    four widths) against the same block on CPU fp32: output, input gradient, all parameter
+    gradients."""
+    import copy
+    from distributed_training_dl_b200.models import Bottleneck
+    from distributed_training_dl_b200.ops import functional as fn
+
+    def cos(a, b):
+        a, b = a.flatten().double(), b.flatten().double()
+        return (torch.dot(a, b) / (a.norm() * b.norm() + 1e-30)).item()
+
+    torch.manual_seed(0)
+    for cin, width, stride, ds, hw in [(64, 64, 1, True, 32), (256, 64, 1, False, 32), (256, 128, 2, True, 32),
+                                       (1024, 512, 2, True, 8), (2048, 512, 1, False, 4)]:
+        cpu = Bottleneck(cin, width, stride, ds)
+        gpu = copy.deepcopy(cpu).cuda()
+        x = torch.randn(8, cin, hw, hw)
+        xc = x.clone().requires_grad_(True)
+        yc = cpu(xc)
+        g = torch.randn_like(yc)
+        yc.backward(g)
+        xn = fn.to_nhwc(x.cuda()).requires_grad_(True)
+        yg = gpu(xn)
+        yg.backward(fn.to_nhwc(g.cuda()))
+        assert cos(_nhwc_to_nchw(yg, yc.shape[1]).cpu(), yc) > 0.999
+        assert cos(_nhwc_to_nchw(xn.grad, cin).cpu(), xc.grad) > 0.99
+        for (n, a), (_, b) in zip(cpu.named_parameters(), gpu.named_parameters()):
+            assert cos(b.grad.cpu(), a.grad) > 0.99, (cin, width, n)
+
+
+def test_resnet50_whole_model():
+    """Whole ResNet-50: loss agrees with the CPU fp32 model and the head gradients match.
+    Deeper gradients of a RANDOM-INIT ResNet-50 are chaotic under bf16 rounding -- stock
+    torchvision + bf16 autocast gives cosine 0.12 (conv1) .. 0.39 (layer4) against its own fp32
+    run (tools/debug_resnet3.py) -- so they are checked block by block above instead."""
     import copy
     from distributed_training_dl_b200.models import resnet50
     torch.manual_seed(0)
     cpu = resnet50(num_classes=100)
     gpu = copy.deepcopy(cpu).cuda()
-    x = torch.randn(4, 3, 64, 64)
-    t = torch.randint(0, 100, (4,))
+    x = torch.randn(8, 3, 128, 128)
+    t = torch.randint(0, 100, (8,))
     lc = F.cross_entropy(cpu(x), t)
     lg = F.cross_entropy(gpu(x.cuda()), t.cuda())
-    assert abs(lc.item() - lg.item()) < 0.1 * max(1.0, abs(lc.item())), (lc.item(), lg.item())
+    assert abs(lc.item() - lg.item()) < 0.05 * max(1.0, abs(lc.item())), (lc.item(), lg.item())
     lc.backward()
     lg.backward()
     for (n, a), (_, b) in zip(cpu.named_parameters(), gpu.named_parameters()):
-        assert b.grad is not None, n
-        ga, gb = a.grad.flatten().double(), b.grad.cpu().flatten().double()
-        if ga.norm() < 1e-5:
-            continue
-        cos = torch.dot(ga, gb) / (ga.norm() * gb.norm() + 1e-30)
-        assert cos > 0.9, (n, cos.item())
+        assert b.grad is not None and torch.isfinite(b.grad).all(), n
+        ratio = (b.grad.norm() / (a.grad.norm() + 1e-30)).item()
+        assert 0.5 < ratio < 2.0, (n, ratio)
+    for n in ("fc.weight", "fc.bias"):
+        ga = dict(cpu.named_parameters())[n].grad.flatten().double()
+        gb = dict(gpu.named_parameters())[n].grad.cpu().flatten().double()
+        assert torch.dot(ga, gb) / (ga.norm() * gb.norm()) > 0.97, n
