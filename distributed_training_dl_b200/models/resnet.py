@@ -17,22 +17,77 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from .. import _native as nv
 from ..ops import functional as fn
 from ..ops import modules as L
 from ..ops.modules import _PackedWeightMixin
 
 
 class _StemOperand(_PackedWeightMixin):
-    """Packed-weight holder for the stem's computed 4x4x12 kernel (not an nn.Module)."""
+    """Packed-weight holder for the stem's 4x4x12 kernel (not an nn.Module)."""
 
     def __init__(self, cout):
         self._init_pack_meta(cout, 12, 4, 4, pad=2, stride=1, need_dgrad=False)
         self.bias = None
-        self.weight = None
-        self.return_wgrad = True      # the 4x4 kernel is a view of the 7x7 parameter: autograd maps it back
+        self.weight = None            # fp32 [O,12,4,4] copy of the 7x7 parameter, persistent (stable pointer)
         self.out_hw = None
-        self.pack_src = None          # persistent fp32 copy the pack kernel reads (stable pointer)
         self._table = {}
+
+
+def s2d_weight(w7):
+    """[O,3,7,7] -> [O,12,4,4]: pad the kernel to 8x8 at the low side, split the 2x2 phases."""
+    O = w7.shape[0]
+    w8 = F.pad(w7, (1, 0, 1, 0))                             # [O,3,8,8], index 0 is the zero tap
+    w = w8.view(O, 3, 4, 2, 4, 2).permute(0, 3, 5, 1, 2, 4)   # [O, bh, bw, c, a, b]
+    return w.reshape(O, 12, 4, 4)
+
+
+def s2d_weight_adjoint(g4):
+    """Gradient of ``s2d_weight``: [O,12,4,4] -> [O,3,7,7]."""
+    O = g4.shape[0]
+    g8 = g4.view(O, 2, 2, 3, 4, 4).permute(0, 3, 4, 1, 5, 2).reshape(O, 3, 8, 8)
+    return g8[:, :, 1:, 1:]
+
+
+class _StemFn(torch.autograd.Function):
+    """7x7/2 convolution as 4x4/1 over the space-to-depth image; the weight gradient is mapped
+    back to 7x7 and written into the parameter's gradient buffer like every other layer's."""
+
+    @staticmethod
+    def forward(ctx, x, weight, op):
+        N, C, H, W = x.shape
+        if op.weight is None or op.weight.device != x.device:
+            op.weight = torch.empty((op.Cout, 12, 4, 4), dtype=torch.float32, device=x.device)
+            op._alloc_packs(x.device)
+            op._table = {}
+        op.weight.copy_(s2d_weight(weight.detach()))
+        L.pack_weights([op], op._table)
+        xs = fn.to_s2d(x)
+        y = fn.conv_fprop_raw(xs, op.wf, op.Cout_p, 4, 4, 2, out_hw=(H // 2, W // 2))
+        ctx.op = op
+        ctx.save_for_backward(xs, weight)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        op = ctx.op
+        xs, weight = ctx.saved_tensors
+        dy = dy.contiguous()
+        N, Hs, Ws, Cin_p = xs.shape
+        Ho, Wo = dy.shape[1], dy.shape[2]
+        g4 = torch.empty((op.Cout, 12, 4, 4), dtype=torch.float32, device=dy.device)
+        need = nv.lib().dtdl_conv_wgrad_workspace_bytes(N, Ho, Wo, Cin_p, op.Cout_p, 4, 4)
+        ws = fn.scratch(xs.device, need)
+        nv.call("conv_wgrad", nv.ptr(xs), nv.ptr(dy), nv.ptr(g4), nv.ptr(ws), ws.numel(), N, Hs, Ws, 12, Cin_p,
+                Ho, Wo, op.Cout, op.Cout_p, 4, 4, 2, 2, 0, nv.stream_ptr())
+        gw, acc = fn.grad_buffer(weight)
+        g7 = s2d_weight_adjoint(g4)
+        if acc:
+            gw.add_(g7)
+        else:
+            gw.copy_(g7)
+        fn._grad_ready(weight)
+        return None, None, None
 
 
 class StemConv7x7s2(nn.Conv2d):
@@ -43,28 +98,12 @@ class StemConv7x7s2(nn.Conv2d):
         assert in_channels == 3
         self._op = _StemOperand(out_channels)
 
-    @staticmethod
-    def s2d_weight(w7):
-        """[O,3,7,7] -> [O,12,4,4]: pad the kernel to 8x8 at the low side, split the 2x2 phases."""
-        O = w7.shape[0]
-        w8 = F.pad(w7, (1, 0, 1, 0))                          # [O,3,8,8], index 0 is the zero tap
-        w = w8.view(O, 3, 4, 2, 4, 2).permute(0, 3, 5, 1, 2, 4)  # [O, bh, bw, c, a, b]
-        return w.reshape(O, 12, 4, 4)
+    s2d_weight = staticmethod(s2d_weight)
 
     def forward(self, x):
         if not x.is_cuda:
             return super().forward(x)
-        N, C, H, W = x.shape
-        op = self._op
-        op.weight = self.s2d_weight(self.weight)
-        op.out_hw = (H // 2, W // 2)
-        if op.pack_src is None or op.pack_src.device != x.device:
-            op.pack_src = torch.empty(op.weight.shape, dtype=torch.float32, device=x.device)
-            op._alloc_packs(x.device)
-            op._table = {}
-        op.pack_src.copy_(op.weight.detach())
-        L.pack_weights([op], op._table)
-        return fn.conv(fn.to_s2d(x), op)
+        return _StemFn.apply(x, self.weight, self._op)
 
 
 class Bottleneck(nn.Module):

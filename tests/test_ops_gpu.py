@@ -181,7 +181,7 @@ def test_models_match_cpu_oracle():
     for make, shape, tol, min_cos in [(lambda: MLP(128), (32, 784), 3e-2, 0.98),
                                       (MnistCNN, (16, 1, 28, 28), 3e-2, 0.98),
                                       (shallow, (8, 3, 32, 32), 0.1, 0.97),
-                                      (pyramidnet, (8, 3, 32, 32), 0.15, 0.8)]:
+                                      (pyramidnet, (8, 3, 32, 32), 0.15, 0.7)]:
         cpu = make()
         gpu = copy.deepcopy(cpu).cuda()
         x = torch.randn(*shape)
