@@ -1,6 +1,7 @@
 """Device timing: CUDA events on the launching stream, max over ranks (never wall clock)."""
 from __future__ import annotations
 
+import os
 import subprocess
 import threading
 import time
@@ -50,57 +51,99 @@ def flush_l2(device=None, nbytes=256 << 20):
 
 
 class ClockSampler:
-    """Samples ``nvidia-smi`` SM clocks / throttle reasons while a timed region runs."""
+    """Samples SM clocks and throttle reasons while a timed region runs.
+
+    Uses NVML (the library behind ``nvidia-smi``) from a background thread every ``period_ms``;
+    falls back to an ``nvidia-smi --query-gpu=... -lms`` subprocess when NVML cannot be loaded.
+    ``summary()`` reports the median SM clock over the samples, the maximum SM clock and the
+    set of slowdown reasons that were active at any sample.
+    """
 
     QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
              "clocks_event_reasons.sw_power_cap")
+    REASON_BITS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+                   0x4: "sw_power_cap", 0x80: "hw_power_brake_slowdown"}
 
-    def __init__(self, gpu_index=0, period_ms=200):
+    def __init__(self, gpu_index=0, period_ms=20):
         self.gpu_index, self.period_ms = gpu_index, period_ms
-        self.proc, self.lines = None, []
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thread = self._proc = None
+
+    def _physical_index(self):
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            try:
+                return int(vis.split(",")[self.gpu_index])
+            except (ValueError, IndexError):
+                pass
+        return self.gpu_index
+
+    def _nvml_loop(self, handle, nvml):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(float(nvml.nvmlDeviceGetClockInfo(handle, nvml.NVML_CLOCK_SM)))
+                try:
+                    mask = nvml.nvmlDeviceGetCurrentClocksEventReasons(handle)
+                except Exception:  # noqa: BLE001  (older bindings spell it ThrottleReasons)
+                    mask = nvml.nvmlDeviceGetCurrentClocksThrottleReasons(handle)
+                for bit, name in self.REASON_BITS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:  # noqa: BLE001
+                break
+            self._stop.wait(self.period_ms / 1e3)
 
     def __enter__(self):
         try:
-            self.proc = subprocess.Popen(
+            import pynvml as nvml
+            nvml.nvmlInit()
+            handle = nvml.nvmlDeviceGetHandleByIndex(self._physical_index())
+            self.max_mhz = float(nvml.nvmlDeviceGetMaxClockInfo(handle, nvml.NVML_CLOCK_SM))
+            self._thread = threading.Thread(target=self._nvml_loop, args=(handle, nvml), daemon=True)
+            self._thread.start()
+            return self
+        except Exception:  # noqa: BLE001
+            pass
+        try:
+            self._proc = subprocess.Popen(
                 ["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
-                 "-i", str(self.gpu_index), "-lms", str(self.period_ms)],
+                 "-i", str(self._physical_index()), "-lms", str(max(self.period_ms, 50))],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
-            self.thread.start()
+            self._thread = threading.Thread(target=self._smi_loop, daemon=True)
+            self._thread.start()
         except OSError:
-            self.proc = None
+            self._proc = None
         return self
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
-
-    def __exit__(self, *exc):
-        if self.proc is not None:
-            self.proc.terminate()
-            try:
-                self.proc.wait(timeout=2)
-            except subprocess.TimeoutExpired:
-                self.proc.kill()
-
-    def summary(self):
-        sm, mx, reasons = [], 0.0, set()
+    def _smi_loop(self):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in self.lines:
+        for line in self._proc.stdout:
             parts = [p.strip() for p in line.split(",")]
             if len(parts) < 7:
                 continue
             try:
-                sm.append(float(parts[0]))
-                mx = max(mx, float(parts[1]))
+                self.samples.append(float(parts[0]))
+                self.max_mhz = max(self.max_mhz or 0.0, float(parts[1]))
             except ValueError:
                 continue
             for name, val in zip(names, parts[3:7]):
                 if val.lower().startswith("active"):
-                    reasons.add(name)
-        sm.sort()
-        # "under load" = upper half of the samples (idle samples sit at the low clock)
-        load = sm[len(sm) // 2:] if sm else []
-        med = load[len(load) // 2] if load else None
-        return {"sm_mhz": med, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm)}
+                    self.reasons.add(name)
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        if self._proc is not None:
+            self._proc.terminate()
+            try:
+                self._proc.wait(timeout=2)
+            except subprocess.TimeoutExpired:
+                self._proc.kill()
+        if self._thread is not None:
+            self._thread.join(timeout=2)
+
+    def summary(self):
+        sm = sorted(self.samples)
+        med = sm[len(sm) // 2] if sm else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(sm)}

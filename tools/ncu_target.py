@@ -18,5 +18,16 @@ for _ in range(4):
     y = fn.conv_fprop_raw(x, conv.wf, conv.Cout_p, 3, 3, 1)
     nv.call("conv_wgrad", nv.ptr(x), nv.ptr(dy), nv.ptr(gw), nv.ptr(ws), ws.numel(), N, hw, hw, cin, conv.Cin_p,
             hw, hw, cout, conv.Cout_p, 3, 3, 1, 1, 0, nv.stream_ptr())
+# bandwidth-bound kernels on the same shape: BN forward (stats + apply) and backward, fused SGD
+from distributed_training_dl_b200.ops import BatchNorm2d
+bn = BatchNorm2d(cout).cuda()
+xb = dy.clone().requires_grad_(True)
+for _ in range(2):
+    yb = bn(xb, relu=True)
+    yb.backward(dy)
+p = torch.randn(1 << 24, device="cuda"); g = torch.randn_like(p); m = torch.zeros_like(p)
+hyper = torch.tensor([0.1, 0.9, 1e-4, 1.0] + [0.0] * 12, device="cuda")
+for _ in range(2):
+    nv.call("local_update", nv.ptr(p), nv.ptr(g), nv.ptr(m), 0, nv.ptr(hyper), p.numel(), 1, nv.stream_ptr())
 torch.cuda.synchronize()
 print("ok", float(y.float().abs().mean()))
