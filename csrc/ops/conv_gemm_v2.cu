@@ -37,7 +37,7 @@ struct ConvV2Args {
   const float* bias;
 };
 
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(256, 2)
 conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const ConvV2Args a) {
   extern __shared__ uint8_t smem_raw[];
@@ -238,7 +238,11 @@ int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, 
   a.n_tile = n_tile;
   const int cols = MS * n_tile;
   a.tmem_cols = cols <= 32 ? 32 : cols <= 64 ? 64 : cols <= 128 ? 128 : cols <= 256 ? 256 : 512;
-  int stages = (220 * 1024) / a.stage_bytes;
+  // Two CTAs per SM whenever two stages fit in half of the shared memory and the grid is deep
+  // enough: one CTA's prologue / epilogue then overlaps the other's main loop.
+  const long long ctas = (long long)N * a.tiles_h * n_tiles;
+  const bool two_per_sm = 2 * a.stage_bytes <= 110 * 1024 && a.tmem_cols <= 256 && ctas > sm_count();
+  int stages = ((two_per_sm ? 110 : 220) * 1024) / a.stage_bytes;
   if (stages > 6) stages = 6;
   const int n_groups = KW * a.chunks;
   if (stages > n_groups) stages = n_groups < 2 ? 2 : n_groups;

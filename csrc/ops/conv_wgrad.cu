@@ -244,6 +244,12 @@ wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int sp
 
 using namespace dtdl;
 
+#include <stdlib.h>
+static int wgrad_waves() {
+  static int w = getenv("DTDL_WGRAD_WAVES") ? atoi(getenv("DTDL_WGRAD_WAVES")) : 2;
+  return w < 1 ? 1 : w;
+}
+
 // Plans the split-K decomposition; shared by the size query and the launch.
 static void wgrad_plan(int N, int Ho, int Wo, int Cin_p, int Cout_p, int KH, int KW, WgradArgs* a,
                        int* splits) {
@@ -264,7 +270,10 @@ static void wgrad_plan(int N, int Ho, int Wo, int Cin_p, int Cout_p, int KH, int
   a->taps = KH * KW;
   const int co_tiles = (Cout_p + 127) / 128;
   const int groups = KH * a->groups_per_row * co_tiles * a->ci_chunks;
-  int sp = (2 * sm_count() + groups - 1) / groups;
+  // few output tiles (narrow layers): one wave of fat CTAs amortises set-up and halves the
+  // partials the reduction has to read; wider layers do better with two waves
+  const int waves = getenv("DTDL_WGRAD_WAVES") ? wgrad_waves() : (groups <= 3 ? 1 : 2);
+  int sp = (waves * sm_count() + groups - 1) / groups;
   if (sp > a->n_ptiles) sp = a->n_ptiles;
   if (sp < 1) sp = 1;
   a->tiles_per_split = (a->n_ptiles + sp - 1) / sp;
