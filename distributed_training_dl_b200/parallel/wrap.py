@@ -17,6 +17,8 @@ bucket logic over ``torch.distributed`` collectives.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 import torch.nn as nn
@@ -25,6 +27,8 @@ from ..ops import functional as fn
 from ..ops.modules import packed_layers
 from . import rendezvous
 from .arena import BufferArena, ParamArena
+
+_NVTX = os.environ.get("DTDL_NVTX") == "1"  # NVTX ranges around bucket launches (Nsight timelines)
 
 
 class Reducer:
@@ -132,6 +136,15 @@ class Reducer:
     def _launch(self, bucket):
         if not self.require_sync:
             return
+        if _NVTX:
+            torch.cuda.nvtx.range_push(f"dtdl.bucket{bucket.index}.{bucket.numel * 4 >> 10}KiB")
+        try:
+            self._launch_impl(bucket)
+        finally:
+            if _NVTX:
+                torch.cuda.nvtx.range_pop()
+
+    def _launch_impl(self, bucket):
         off_b, n = bucket.offset * 4, bucket.numel
         a = self.arena
         if self.peer is not None and self.world > 1:
