@@ -79,25 +79,26 @@ class _ShardLoss(torch.autograd.Function):
 
     The kernel adds this shard's share of the mean loss and its correct-prediction count into
     ``stats`` -- a 2-float buffer that may live on another GPU -- and produces dlogits scaled by
-    1/total, so summing shard gradients over replicas gives the global-batch gradient.
+    world/total: the reducer then averages over the ``world`` replicas, which yields exactly the
+    mean gradient over the global batch even when the shards are unequal.
     """
 
     @staticmethod
-    def forward(ctx, logits, targets_ptr, stats_ptr, total):
+    def forward(ctx, logits, targets_ptr, stats_ptr, total, world):
         # targets / stats are raw device pointers (GPU 0 memory): handing GPU-0 tensors to
         # autograd would make the engine synchronise GPU 0's streams with this replica's
         logits = logits.contiguous()
         n, C = logits.shape
         dl = torch.empty_like(logits)
         nv.call("softmax_ce", nv.ptr(logits), targets_ptr, stats_ptr, 0, nv.ptr(dl), n, C, C,
-                1.0 / total, 1.0 / total, nv.stream_ptr())
+                1.0 / total, float(world) / total, nv.stream_ptr())
         ctx.save_for_backward(dl)
         return torch.zeros((), device=logits.device)
 
     @staticmethod
     def backward(ctx, g):
         (dl,) = ctx.saved_tensors
-        return dl, None, None, None
+        return dl, None, None, None, None
 
 
 class DataParallel(nn.Module):
@@ -287,7 +288,7 @@ class DataParallelStep:
         opt._hyper_devs[g].copy_(opt._hyper_host, non_blocking=True)
         out = m.run_replica_body(g, self._sx[lo:hi])
         logits = fn.to_f32(out, m.out_features)
-        loss = _ShardLoss.apply(logits, self._st[lo:hi].data_ptr(), self._stats.data_ptr(), self._sx.shape[0])
+        loss = _ShardLoss.apply(logits, self._st[lo:hi].data_ptr(), self._stats.data_ptr(), self._sx.shape[0], m.world)
         for p in m.arenas[g].params:
             p._dtdl_fresh = True
         loss.backward()

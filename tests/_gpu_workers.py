@@ -202,4 +202,28 @@ def data_parallel_engine(outdir):
     assert replicas_identical(), "replicas diverged (graph)"
     sd = opt.state_dict()
     assert "momentum_buffer" in sd["state"][0]
+    # BN-free model: k graph steps == single-process fp32 SGD on the whole batch
+    from distributed_training_dl_b200.models import MLP
+    torch.manual_seed(3)
+    mlp = MLP(n_units=64)
+    ref = copy.deepcopy(mlp)
+    dp2 = dtdl.DataParallel(mlp, device_ids=list(range(ndev)))
+    opt2 = dtdl.FusedSGD(dp2.parameters(), lr=0.05, momentum=0.9)
+    ropt = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9)
+    step2 = dtdl.DataParallelStep(dp2, opt2, graph=True, warmup=1)
+    g = torch.Generator().manual_seed(11)
+    for it in range(4):
+        xb = torch.randn(16 * ndev, 784, generator=g)
+        tb = torch.randint(0, 10, (16 * ndev,), generator=g)
+        stats = step2(xb.pin_memory(), tb.pin_memory())
+        rl = F.cross_entropy(ref(xb), tb)
+        ropt.zero_grad()
+        rl.backward()
+        ropt.step()
+        assert abs(float(stats[0]) - rl.item()) < 3e-2, (float(stats[0]), rl.item())
+    for d in range(ndev):
+        torch.cuda.synchronize(d)
+    for (n_, p), q in zip(dp2.module.named_parameters(), ref.parameters()):
+        err = (p.detach().cpu() - q).abs().max().item()
+        assert err < 5e-3, (n_, err)
     open(os.path.join(outdir, "ok_dp"), "w").write("ok")
