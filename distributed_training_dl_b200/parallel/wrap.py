@@ -92,6 +92,10 @@ class Reducer:
         if self._pending is not None and self._next not in (0, len(self.arena.buckets)):
             self.flush()
         self._pending = [len(b.params) for b in self.arena.buckets]
+        self._seen = set()
+        # the stream the user's step runs on: end-of-backward joins are applied to THIS stream (the
+        # autograd callback may run on an engine thread whose current stream is a different one)
+        self._user_stream = torch.cuda.current_stream(self.device) if self.device.type == "cuda" else None
         self._next = 0
         self._launched_any = False
         if self.optimizer is not None:
@@ -115,6 +119,12 @@ class Reducer:
             # p.grad holds the averaged gradient when backward() returns (DDP's contract)
             self._callback_queued = True
             torch.autograd.Variable._execution_engine.queue_callback(self._backward_done)
+        # A parameter can be announced twice in one backward (by the kernel that wrote its
+        # gradient AND by autograd's post-accumulate hook, which torch also fires for parameters
+        # whose Function returned no gradient): count it once.
+        if id(p) in self._seen:
+            return
+        self._seen.add(id(p))
         b = self.arena.bucket_of[id(p)]
         self._pending[b] -= 1
         while self._next < len(self.arena.buckets) and self._pending[self._next] <= 0:
@@ -181,6 +191,8 @@ class Reducer:
         a = self.arena
         if self.peer is not None and self.world > 1:
             torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+            if getattr(self, "_user_stream", None) is not None:
+                self._user_stream.wait_stream(self.comm_stream)
         elif self.world > 1:
             for work, bucket in self._works:
                 work.wait()

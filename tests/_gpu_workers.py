@@ -227,3 +227,43 @@ def data_parallel_engine(outdir):
         err = (p.detach().cpu() - q).abs().max().item()
         assert err < 5e-3, (n_, err)
     open(os.path.join(outdir, "ok_dp"), "w").write("ok")
+
+
+def ddp_variants(i, world, outdir, backend):
+    """Same bucket logic over other back ends / optimizers: NCCL collectives, a stock torch
+    optimizer behind wrap(), and gradient accumulation with no_sync()."""
+    import distributed_training_dl_b200 as dtdl
+    from distributed_training_dl_b200.models import MLP
+    comm = dtdl.init(backend=backend)
+    dev = comm.device
+    g = torch.Generator().manual_seed(21)
+    for opt_kind in ("fused", "torch"):
+        torch.manual_seed(5)
+        mlp = MLP(n_units=48)
+        ref = copy.deepcopy(mlp)
+        net = dtdl.wrap(mlp.to(dev))
+        if opt_kind == "fused":
+            opt = dtdl.FusedSGD(net.parameters(), lr=0.05, momentum=0.9)
+        else:
+            opt = torch.optim.SGD(net.parameters(), lr=0.05, momentum=0.9)
+        ropt = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9)
+        for it in range(3):
+            xs = torch.randn(world, 2, 16, 784, generator=g)      # two micro-batches per rank
+            ts = torch.randint(0, 10, (world, 2, 16), generator=g)
+            opt.zero_grad()
+            with net.no_sync():                                    # accumulate locally, no collective
+                (F.cross_entropy(net(xs[i, 0].to(dev)), ts[i, 0].to(dev)) / 2).backward()
+            (F.cross_entropy(net(xs[i, 1].to(dev)), ts[i, 1].to(dev)) / 2).backward()
+            opt.step()
+            ropt.zero_grad()
+            F.cross_entropy(ref(xs.reshape(-1, 784)), ts.reshape(-1)).backward()
+            ropt.step()
+        torch.cuda.synchronize()
+        for (n_, p), q in zip(net.module.named_parameters(), ref.parameters()):
+            err = (p.detach().cpu() - q).abs().max().item()
+            assert err < 5e-3, (backend, opt_kind, n_, err)
+        chk = torch.cat([p.detach().flatten()[:32] for p in net.parameters()]).cpu()
+        alls = comm.allgather_object(chk)
+        assert all(torch.equal(alls[0], a) for a in alls), (backend, opt_kind, max((alls[0] - a).abs().max().item() for a in alls))
+    _ok(outdir, i)
+    dtdl.shutdown()

@@ -6,7 +6,7 @@ import torch
 
 import distributed_training_dl_b200 as dtdl
 
-from _gpu_workers import collectives, ddp_training
+from _gpu_workers import collectives, ddp_training, ddp_variants
 
 pytestmark = pytest.mark.gpu
 
@@ -39,3 +39,10 @@ def test_data_parallel_engine(tmp_path):
     code = f"import sys; sys.path.insert(0, {here!r}); import _gpu_workers as w; w.data_parallel_engine({str(tmp_path)!r})"
     res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
     assert res.returncode == 0 and os.path.exists(tmp_path / "ok_dp"), res.stdout[-2000:] + res.stderr[-4000:]
+
+
+@pytest.mark.parametrize("backend", ["b200", "nccl"])
+def test_ddp_backends_optimizers_no_sync(tmp_path, backend):
+    world = _world()
+    dtdl.spawn(ddp_variants, nprocs=world, args=(world, str(tmp_path), backend))
+    assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
