@@ -64,6 +64,21 @@ int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_
   return 0;
 }
 
+int multicast_supported(int dev) {
+  // CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED through the runtime's driver entry point (no -lcuda)
+  typedef CUresult (*GetAttrFn)(int*, CUdevice_attribute, CUdevice);
+  typedef CUresult (*GetDevFn)(CUdevice*, int);
+  void *pa = nullptr, *pd = nullptr;
+  cudaDriverEntryPointQueryResult q;
+  if (cudaGetDriverEntryPoint("cuDeviceGetAttribute", &pa, cudaEnableDefault, &q) != cudaSuccess || !pa) return -1;
+  if (cudaGetDriverEntryPoint("cuDeviceGet", &pd, cudaEnableDefault, &q) != cudaSuccess || !pd) return -1;
+  CUdevice d;
+  if (reinterpret_cast<GetDevFn>(pd)(&d, dev) != CUDA_SUCCESS) return -1;
+  int v = 0;
+  if (reinterpret_cast<GetAttrFn>(pa)(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, d) != CUDA_SUCCESS) return -1;
+  return v;
+}
+
 int sm_count() {
   static int n = 0;
   if (n == 0) {

@@ -43,4 +43,7 @@ int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_
 
 int sm_count();
 
+// 1 / 0 = the device can / cannot join an NVLS multicast object, -1 = query failed.
+int multicast_supported(int dev);
+
 }  // namespace dtdl

@@ -164,6 +164,10 @@ class PeerComm:
             bufs.append(b)
         return bufs
 
+    def multicast_supported(self) -> bool:
+        """NVLS probe: can this GPU join a multicast object (``multimem`` collectives)?"""
+        return nv.lib().dtdl_multicast_supported(self.device.index or 0) == 1
+
     # ------------------------------------------------------------------ collectives
     def _stream(self, stream):
         return (stream or torch.cuda.current_stream(self.device)).cuda_stream

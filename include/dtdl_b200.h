@@ -119,6 +119,9 @@ int dtdl_ipc_get_handle(void* ptr, void* out64);
 int dtdl_ipc_open_handle(const void* in64, void** ptr);
 int dtdl_ipc_close_handle(void* ptr);
 int dtdl_enable_peer_access(int dev, int peer);
+/* 1 / 0: device can / cannot join an NVLS multicast object (CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED),
+ * -1: query failed.  The shipped collectives are the P2P variants; multicast ones are gated on this. */
+int dtdl_multicast_supported(int device);
 int dtdl_comm_barrier(void* handle, void* stream);
 int dtdl_comm_allreduce(void* handle, void* const* grads, void* const* dst, long long offset_bytes,
                         long long n, float scale, int two_shot, int max_blocks, void* stream);
