@@ -182,6 +182,15 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t 
   return d;
 }
 
+// The tcgen05.mma issue loop runs on ONE thread; every scalar instruction in it is on the
+// critical path of the tensor pipe (measured: two integer divisions per MMA doubled a kernel's
+// time).  So descriptors are built once per stage and advanced with a single 64-bit add: the
+// start-address field holds (addr >> 4) in the low bits, and the operand tiles never cross the
+// 256 KB shared window, so adding (bytes >> 4) cannot carry into the other fields.
+__device__ __forceinline__ uint64_t umma_desc_advance(uint64_t desc, uint32_t bytes) {
+  return desc + (uint64_t)(bytes >> 4);
+}
+
 // Instruction descriptor for kind::f16 with bf16 A/B and fp32 D.
 //   c_format=F32 (1<<4), a_format=BF16 (1<<7), b_format=BF16 (1<<10),
 //   a_major bit 15, b_major bit 16 (0 = K-major, 1 = MN-major),

@@ -122,18 +122,20 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 1) {
     if (elect_one()) {
       const uint32_t idesc = umma_idesc_bf16(128, a.n_tile, 0, 0);
-      const uint32_t sA_addr = smem_u32(sA), sB_addr = smem_u32(sB);
+      const uint64_t adesc0 = umma_smem_desc(smem_u32(sA), 16, 1024);
+      const uint64_t bdesc0 = umma_smem_desc(smem_u32(sB), 16, 1024);
       int stage = 0, phase = 0;
       for (int kb = 0; kb < n_kblocks; ++kb) {
         const int c = kb % a.chunks;
         mbar_wait(&full[stage], phase, 2);
         tc_fence_after();
         const int nsl = (c == a.chunks - 1) ? a.last_slices : 4;
-        for (int k = 0; k < nsl; ++k) {
-          const uint64_t ad = umma_smem_desc(sA_addr + stage * kAStage + k * 32, 16, 1024);
-          const uint64_t bd = umma_smem_desc(sB_addr + stage * a.b_stage_bytes + k * 32, 16, 1024);
-          umma_bf16(tmem_base, ad, bd, idesc, (kb > 0 || k > 0) ? 1u : 0u);
-        }
+        const uint64_t ad = umma_desc_advance(adesc0, (uint32_t)(stage * kAStage));
+        const uint64_t bd = umma_desc_advance(bdesc0, (uint32_t)(stage * a.b_stage_bytes));
+        umma_bf16(tmem_base, ad, bd, idesc, kb > 0 ? 1u : 0u);
+#pragma unroll
+        for (int k = 1; k < 4; ++k)
+          if (k < nsl) umma_bf16(tmem_base, umma_desc_advance(ad, k * 32), umma_desc_advance(bd, k * 32), idesc, 1u);
         umma_commit(&empty[stage]);
         if (++stage == a.stages) {
           stage = 0;

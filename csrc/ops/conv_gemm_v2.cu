@@ -100,23 +100,28 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   } else if (warp == 1) {
     if (elect_one()) {
       const uint32_t idesc = umma_idesc_bf16(128, a.n_tile, 0, 0);
-      const uint32_t base = smem_u32(smem);
+      const uint64_t desc0 = umma_smem_desc(smem_u32(smem), 16, 1024);
+      const uint32_t row_bytes = (uint32_t)(a.BW * 128);          // one image row of the halo box
+      const uint32_t sub_bytes = (uint32_t)(a.BH * a.BW * 128);   // one 128-pixel sub-tile
       int stage = 0, phase = 0;
       for (int g = 0; g < n_groups; ++g) {
         const int c = g % a.chunks;
         mbar_wait(&full[stage], phase, 22);
         tc_fence_after();
         const int nsl = (c == a.chunks - 1) ? a.last_slices : 4;
-        const uint32_t sa = base + stage * a.stage_bytes;
-        const uint32_t sb = sa + a.a_stage_bytes;
+        const uint64_t sa = umma_desc_advance(desc0, (uint32_t)(stage * a.stage_bytes));
+        const uint64_t sb = umma_desc_advance(sa, (uint32_t)a.a_stage_bytes);
         for (int m = 0; m < a.MS; ++m) {
+          uint64_t ad = umma_desc_advance(sa, (uint32_t)(m * sub_bytes));
+          uint64_t bd = sb;
           for (int r = 0; r < a.KH; ++r) {
-            const uint32_t arow = sa + (uint32_t)((m * a.BH + r) * a.BW) * 128u;
-            for (int k = 0; k < nsl; ++k) {
-              const uint64_t ad = umma_smem_desc(arow + k * 32, 16, 1024);
-              const uint64_t bd = umma_smem_desc(sb + r * a.b_box_bytes + k * 32, 16, 1024);
-              umma_bf16(tmem_base + m * a.n_tile, ad, bd, idesc, (g > 0 || r > 0 || k > 0) ? 1u : 0u);
-            }
+            umma_bf16(tmem_base + m * a.n_tile, ad, bd, idesc, (g > 0 || r > 0) ? 1u : 0u);
+#pragma unroll
+            for (int k = 1; k < 4; ++k)
+              if (k < nsl)
+                umma_bf16(tmem_base + m * a.n_tile, umma_desc_advance(ad, k * 32), umma_desc_advance(bd, k * 32), idesc, 1u);
+            ad = umma_desc_advance(ad, row_bytes);
+            bd = umma_desc_advance(bd, (uint32_t)a.b_box_bytes);
           }
         }
         umma_commit(&empty[stage]);

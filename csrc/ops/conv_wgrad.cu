@@ -40,12 +40,14 @@ struct WgradArgs {
   int Cout_p, Cin_w, taps;
   int stages, stage_bytes;
   int zero_fill;
+  int col_mode;    // 1: CTA owns one filter COLUMN; its KH filter rows are views of one x halo box
+  int KH, x_off, halo_rows;
   float* ws;
 };
 
 static constexpr int kBox = 128 * 128;  // [128 pixel rows][64 bf16]
 
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(256, 2)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ CUtensorMap tmX,
                   const WgradArgs a) {
   extern __shared__ uint8_t smem_raw[];
@@ -60,9 +62,12 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constan
   const int lane = threadIdx.x & 31;
 
   const int split = blockIdx.x;
-  const int r = blockIdx.y / a.groups_per_row;
-  const int s0 = (blockIdx.y % a.groups_per_row) * 3;
-  const int ns = (a.KW - s0) < 3 ? (a.KW - s0) : 3;
+  // row mode : CTA = (filter row r, up to 3 filter columns s0..), one shifted x box per column
+  // col mode : CTA = filter column s0, all KH filter rows, ONE x halo box; the operand of filter
+  //            row r is that box viewed r image rows (r*BW*128 bytes, 1 KB aligned) further down
+  const int r = a.col_mode ? 0 : blockIdx.y / a.groups_per_row;
+  const int s0 = a.col_mode ? blockIdx.y : (blockIdx.y % a.groups_per_row) * 3;
+  const int ns = a.col_mode ? a.KH : ((a.KW - s0) < 3 ? (a.KW - s0) : 3);
   const int co_tile = blockIdx.z / a.ci_chunks;
   const int ci_chunk = blockIdx.z % a.ci_chunks;
   const int co0 = co_tile * 128, ci0 = ci_chunk * 64;
@@ -103,7 +108,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constan
 
   if (warp == 0) {
     if (elect_one()) {
-      const uint32_t tx = (uint32_t)(a.rows * 128 * (a.m_boxes + ns));
+      const uint32_t tx = a.col_mode ? (uint32_t)(a.rows * 128 * a.m_boxes + a.halo_rows * 128)
+                                     : (uint32_t)(a.rows * 128 * (a.m_boxes + ns));
       int stage = 0, phase = 0;
       for (int pt = pt_begin; pt < pt_end; ++pt) {
         int t = pt;
@@ -116,9 +122,13 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constan
         mbar_arrive_expect_tx(&full[stage], tx);
         for (int b = 0; b < a.m_boxes; ++b)
           tma_load_4d(st + b * kBox, &tmDy, &full[stage], co0 + b * 64, w0, h0, n0);
-        for (int s = 0; s < ns; ++s)
-          tma_load_4d(st + (2 + s) * kBox, &tmX, &full[stage], ci0, w0 + s0 + s - a.pad_w,
-                      h0 + r - a.pad_h, n0);
+        if (a.col_mode) {
+          tma_load_4d(st + a.x_off, &tmX, &full[stage], ci0, w0 + s0 - a.pad_w, h0 - a.pad_h, n0);
+        } else {
+          for (int s = 0; s < ns; ++s)
+            tma_load_4d(st + (2 + s) * kBox, &tmX, &full[stage], ci0, w0 + s0 + s - a.pad_w,
+                        h0 + r - a.pad_h, n0);
+        }
         if (++stage == a.stages) {
           stage = 0;
           phase ^= 1;
@@ -128,17 +138,29 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constan
   } else if (warp == 1) {
     if (elect_one()) {
       const uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);
-      const uint32_t base = smem_u32(smem);
+      const uint64_t desc0 = umma_smem_desc(smem_u32(smem), kBox, 1024);
+      uint32_t koff[8];  // byte offset of K slice k inside the B operand (computed once)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int kpi = (a.BW * a.BH) >> 4;
+        koff[k] = a.col_mode ? (uint32_t)(((k / kpi) * (a.BH + a.KH - 1) * a.BW) * 128 + (k % kpi) * 2048)
+                             : (uint32_t)(k * 2048);
+      }
       int stage = 0, phase = 0;
       for (int i = 0; i < n_steps; ++i) {
         mbar_wait(&full[stage], phase, 12);
         tc_fence_after();
-        const uint32_t st = base + stage * a.stage_bytes;
+        const uint64_t ad0 = umma_desc_advance(desc0, (uint32_t)(stage * a.stage_bytes));
         for (int s = 0; s < ns; ++s) {
-          for (int k = 0; k < a.kslices; ++k) {
-            const uint64_t ad = umma_smem_desc(st + k * 2048, kBox, 1024);
-            const uint64_t bd = umma_smem_desc(st + (2 + s) * kBox + k * 2048, kBox, 1024);
-            umma_bf16(tmem_base + s * 64, ad, bd, idesc, (i > 0 || k > 0) ? 1u : 0u);
+          // B operand of accumulator s: row mode = its own shifted box; col mode = the halo box
+          // viewed s image rows further down (koff[] already holds the per-slice image jumps)
+          const uint64_t bd0 = umma_desc_advance(ad0, a.col_mode ? (uint32_t)(a.x_off + s * a.BW * 128)
+                                                                : (uint32_t)((2 + s) * kBox));
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            if (k < a.kslices)
+              umma_bf16(tmem_base + s * 64, umma_desc_advance(ad0, k * 2048), umma_desc_advance(bd0, koff[k]),
+                        idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
         }
         umma_commit(&empty[stage]);
@@ -157,7 +179,7 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constan
     tc_fence_after();
     const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
     for (int s = 0; s < ns; ++s) {
-      const int t = r * a.KW + s0 + s;
+      const int t = a.col_mode ? s * a.KW + s0 : r * a.KW + s0 + s;
       float* dst =
           a.ws + (((size_t)split * a.taps + t) * a.Cout_p + (valid ? co : 0)) * a.Cin_w + ci0;
       for (int j = 0; j < 4; ++j) {
@@ -268,8 +290,13 @@ static void wgrad_plan(int N, int Ho, int Wo, int Cin_p, int Cout_p, int KH, int
   a->Cout_p = Cout_p;
   a->m_boxes = Cout_p <= 64 ? 1 : 2;
   a->taps = KH * KW;
+  a->KH = KH;
+  static const bool no_col = getenv("DTDL_WGRAD_ROWMODE") != nullptr;
+  a->col_mode = (!no_col && a->BW % 8 == 0 && (a->BW * a->BH) % 16 == 0 && a->rows == 128 && KH <= 4 && KH > 1) ? 1 : 0;
+  a->halo_rows = a->BNi * (a->BH + KH - 1) * a->BW;
+  a->x_off = a->m_boxes * kBox;
   const int co_tiles = (Cout_p + 127) / 128;
-  const int groups = KH * a->groups_per_row * co_tiles * a->ci_chunks;
+  const int groups = (a->col_mode ? KW : KH * a->groups_per_row) * co_tiles * a->ci_chunks;
   // few output tiles (narrow layers): one wave of fat CTAs amortises set-up and halves the
   // partials the reduction has to read; wider layers do better with two waves
   const int waves = getenv("DTDL_WGRAD_WAVES") ? wgrad_waves() : (groups <= 3 ? 1 : 2);
@@ -306,10 +333,15 @@ extern "C" int dtdl_conv_wgrad(const void* x, const void* dy, float* dw, void* w
   DTDL_REQUIRE(workspace != nullptr && workspace_bytes >= need,
                "wgrad workspace too small (see dtdl_conv_wgrad_workspace_bytes)");
   a.ws = reinterpret_cast<float*>(workspace);
-  a.stage_bytes = 5 * kBox;  // 2 dy boxes + 3 shifted x boxes
-  a.stages = 2;
+  if (a.col_mode) {
+    a.stage_bytes = a.x_off + (a.halo_rows * 128 + 1023) / 1024 * 1024;  // dy box(es) + x halo box
+    a.stages = a.stage_bytes <= 40 * 1024 ? 3 : 2;
+  } else {
+    a.stage_bytes = 5 * kBox;  // 2 dy boxes + 3 shifted x boxes
+    a.stages = 2;
+  }
   const int steps = a.tiles_per_split;
-  if (steps < 2) a.stages = 1;
+  if (steps < a.stages) a.stages = steps < 1 ? 1 : steps;
 
   CUtensorMap tmDy, tmX;
   {
@@ -322,7 +354,7 @@ extern "C" int dtdl_conv_wgrad(const void* x, const void* dy, float* dw, void* w
   {
     uint64_t dims[4] = {(uint64_t)Cin_p, (uint64_t)W, (uint64_t)H, (uint64_t)N};
     uint64_t str[3] = {(uint64_t)Cin_p * 2, (uint64_t)W * Cin_p * 2, (uint64_t)H * W * Cin_p * 2};
-    uint32_t box[4] = {64, (uint32_t)a.BW, (uint32_t)a.BH, (uint32_t)a.BNi};
+    uint32_t box[4] = {64, (uint32_t)a.BW, (uint32_t)(a.col_mode ? a.BH + KH - 1 : a.BH), (uint32_t)a.BNi};
     if (encode_tmap_bf16(&tmX, x, 4, dims, str, box)) return 1;
   }
   const size_t smem = (size_t)a.stages * a.stage_bytes + 1024 + (2 * a.stages + 1) * 8 + 16;
@@ -335,7 +367,7 @@ extern "C" int dtdl_conv_wgrad(const void* x, const void* dy, float* dw, void* w
     attr_set[dev & 63] = true;
   }
   const int co_tiles = (Cout_p + 127) / 128;
-  dim3 grid(splits, KH * a.groups_per_row, co_tiles * a.ci_chunks);
+  dim3 grid(splits, a.col_mode ? KW : KH * a.groups_per_row, co_tiles * a.ci_chunks);
   conv_wgrad_kernel<<<grid, 256, smem, stream>>>(tmDy, tmX, a);
   DTDL_CHECK_CUDA(cudaGetLastError());
 
