@@ -25,6 +25,7 @@
 #include "../common/host.h"
 #include "../common/ptx.cuh"
 #include "../../include/dtdl_b200.h"
+#include "epilogue.cuh"
 
 #include <stdlib.h>
 
@@ -46,6 +47,7 @@ struct ConvGemmArgs {
   int flags;  // 1 = ReLU, 2 = fp32 output
   void* y;
   const float* bias;
+  float* stats;  // optional [2*Cout_p]: per-channel sum / sum of squares of y (pre-zeroed)
 };
 
 static constexpr int kAStage = 128 * 128;  // 128 pixel rows x 64 bf16
@@ -156,6 +158,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const bool relu = a.flags & 1;
     const bool f32 = a.flags & 2;
 
+    __shared__ float s_sums[512];
+    const int etid = threadIdx.x - 128;
+    if (a.stats != nullptr) epilogue_stats_init(s_sums, a.n_tile, etid);
     mbar_wait(tmem_full, 0, 3);
     tc_fence_after();
     const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
@@ -164,7 +169,6 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       tmem_ld16(lane_base + j * 16, v);
       tmem_ld_wait();
       const int col0 = nt * a.n_tile + j * 16;
-      if (!valid) continue;
       float f[16];
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
@@ -172,6 +176,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (a.bias != nullptr && col0 + i < a.Cout_p) f[i] += a.bias[col0 + i];
         if (relu) f[i] = fmaxf(f[i], 0.f);
       }
+      if (a.stats != nullptr) epilogue_col_stats(f, valid, lane, s_sums, a.n_tile, j * 16);
+      if (!valid) continue;
       if (f32) {
         float* out = reinterpret_cast<float*>(a.y) + pix * a.Cout_p + col0;
 #pragma unroll
@@ -196,6 +202,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
     }
+    if (a.stats != nullptr) epilogue_stats_flush(s_sums, a.stats, a.n_tile, nt * a.n_tile, a.Cout_p, etid);
   }
 
   tc_fence_before();
@@ -221,9 +228,9 @@ void choose_pixel_tile(int N, int Ho, int Wo, int* BW, int* BH, int* BNi) {
   *BNi = bn;
 }
 
-int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, int N, int H, int W,
-                  int Cin_p, int Ho, int Wo, int Cout_p, int KH, int KW, int pad_h, int pad_w,
-                  int flags, cudaStream_t stream);
+int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, float* stats, int N,
+                  int H, int W, int Cin_p, int Ho, int Wo, int Cout_p, int KH, int KW, int pad_h,
+                  int pad_w, int flags, cudaStream_t stream);
 
 }  // namespace dtdl
 
@@ -232,6 +239,14 @@ using namespace dtdl;
 extern "C" int dtdl_conv_fprop(const void* x, const void* wpack, void* y, const float* bias, int N,
                                int H, int W, int Cin_p, int Ho, int Wo, int Cout_p, int KH, int KW,
                                int pad_h, int pad_w, int flags, void* stream_) {
+  return dtdl_conv_fprop_stats(x, wpack, y, bias, nullptr, N, H, W, Cin_p, Ho, Wo, Cout_p, KH, KW, pad_h,
+                               pad_w, flags, stream_);
+}
+
+extern "C" int dtdl_conv_fprop_stats(const void* x, const void* wpack, void* y, const float* bias,
+                                     float* stats, int N, int H, int W, int Cin_p, int Ho, int Wo,
+                                     int Cout_p, int KH, int KW, int pad_h, int pad_w, int flags,
+                                     void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   DTDL_REQUIRE(Cin_p % 8 == 0 && Cout_p % 8 == 0, "channel counts must be padded to 8");
   // Ho / Wo may be smaller than the full stride-1 output (asymmetric padding: the caller
@@ -240,7 +255,7 @@ extern "C" int dtdl_conv_fprop(const void* x, const void* wpack, void* y, const 
                "output size does not match a stride-1 convolution");
   static const bool force_v1 = getenv("DTDL_CONV_V1") != nullptr;
   if (!force_v1) {
-    const int rc = conv_fprop_v2(x, wpack, y, bias, N, H, W, Cin_p, Ho, Wo, Cout_p, KH, KW, pad_h,
+    const int rc = conv_fprop_v2(x, wpack, y, bias, stats, N, H, W, Cin_p, Ho, Wo, Cout_p, KH, KW, pad_h,
                                  pad_w, flags, stream);
     if (rc >= 0) return rc;  // launched (0) or failed (>0); -1 = shape not covered, fall through
   }
@@ -278,9 +293,9 @@ extern "C" int dtdl_conv_fprop(const void* x, const void* wpack, void* y, const 
   const int stage_bytes = kAStage + a.b_stage_bytes;
   // Many small tiles: keep shared memory under half an SM so two CTAs are resident and one
   // tile's epilogue overlaps the other's main loop.  Few big tiles: one deep pipeline.
-  const bool two_per_sm = (long long)m_tiles * n_tiles > sm_count() && 3 * stage_bytes <= 110 * 1024 &&
+  const bool two_per_sm = (long long)m_tiles * n_tiles > sm_count() && 3 * stage_bytes <= 108 * 1024 &&
                           a.tmem_cols <= 256;
-  int stages = ((two_per_sm ? 110 : 200) * 1024) / stage_bytes;
+  int stages = ((two_per_sm ? 108 : 200) * 1024) / stage_bytes;
   if (stages > 8) stages = 8;
   const int n_kblocks = a.taps * a.chunks;
   if (stages > n_kblocks) stages = n_kblocks < 2 ? 2 : n_kblocks;
@@ -288,6 +303,7 @@ extern "C" int dtdl_conv_fprop(const void* x, const void* wpack, void* y, const 
   a.flags = flags;
   a.y = y;
   a.bias = bias;
+  a.stats = stats;
 
   CUtensorMap tmA, tmB;
   {
@@ -309,7 +325,7 @@ extern "C" int dtdl_conv_fprop(const void* x, const void* wpack, void* y, const 
   DTDL_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
     DTDL_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));  // 227 KB less the static epilogue accumulators
     attr_set[dev & 63] = true;
   }
   dim3 grid(m_tiles, n_tiles);

@@ -20,6 +20,7 @@
 #include "../common/host.h"
 #include "../common/ptx.cuh"
 #include "../../include/dtdl_b200.h"
+#include "epilogue.cuh"
 
 namespace dtdl {
 
@@ -35,6 +36,7 @@ struct ConvV2Args {
   int flags;
   void* y;
   const float* bias;
+  float* stats;
 };
 
 __global__ void __launch_bounds__(256, 2)
@@ -139,6 +141,9 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int hi = row / a.BW;
     const bool relu = a.flags & 1;
     const bool f32 = a.flags & 2;
+    __shared__ float s_sums[512];
+    const int etid = threadIdx.x - 128;
+    if (a.stats != nullptr) epilogue_stats_init(s_sums, a.n_tile, etid);
     mbar_wait(tmem_full, 0, 23);
     tc_fence_after();
     const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
@@ -151,7 +156,6 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         tmem_ld16(lane_base + m * a.n_tile + j * 16, v);
         tmem_ld_wait();
         const int col0 = nt * a.n_tile + j * 16;
-        if (!valid) continue;
         float f[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
@@ -159,6 +163,8 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (a.bias != nullptr && col0 + i < a.Cout_p) f[i] += a.bias[col0 + i];
           if (relu) f[i] = fmaxf(f[i], 0.f);
         }
+        if (a.stats != nullptr) epilogue_col_stats(f, valid, lane, s_sums, a.n_tile, j * 16);
+        if (!valid) continue;
         if (f32) {
           float* out = reinterpret_cast<float*>(a.y) + pix * a.Cout_p + col0;
 #pragma unroll
@@ -184,6 +190,7 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
     }
+    if (a.stats != nullptr) epilogue_stats_flush(s_sums, a.stats, a.n_tile, nt * a.n_tile, a.Cout_p, etid);
   }
 
   tc_fence_before();
@@ -193,9 +200,9 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
 // Returns 0 when launched, -1 when the shape does not fit this kernel (caller falls back to
 // the per-tap kernel), >0 on error.
-int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, int N, int H, int W,
-                  int Cin_p, int Ho, int Wo, int Cout_p, int KH, int KW, int pad_h, int pad_w,
-                  int flags, cudaStream_t stream) {
+int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, float* stats, int N,
+                  int H, int W, int Cin_p, int Ho, int Wo, int Cout_p, int KH, int KW, int pad_h,
+                  int pad_w, int flags, cudaStream_t stream) {
   if (Wo % 8 != 0 || Wo > 128 || 128 % Wo != 0) return -1;
   const int BW = Wo, BH = 128 / Wo;
   if (Ho < BH) return -1;
@@ -246,8 +253,8 @@ int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, 
   // Two CTAs per SM whenever two stages fit in half of the shared memory and the grid is deep
   // enough: one CTA's prologue / epilogue then overlaps the other's main loop.
   const long long ctas = (long long)N * a.tiles_h * n_tiles;
-  const bool two_per_sm = 2 * a.stage_bytes <= 110 * 1024 && a.tmem_cols <= 256 && ctas > sm_count();
-  int stages = ((two_per_sm ? 110 : 220) * 1024) / a.stage_bytes;
+  const bool two_per_sm = 2 * a.stage_bytes <= 108 * 1024 && a.tmem_cols <= 256 && ctas > sm_count();
+  int stages = ((two_per_sm ? 108 : 220) * 1024) / a.stage_bytes;
   if (stages > 6) stages = 6;
   const int n_groups = KW * a.chunks;
   if (stages > n_groups) stages = n_groups < 2 ? 2 : n_groups;
@@ -255,6 +262,7 @@ int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, 
   a.flags = flags;
   a.y = y;
   a.bias = bias;
+  a.stats = stats;
 
   CUtensorMap tmA, tmB;
   {
@@ -276,7 +284,7 @@ int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, 
   DTDL_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
     DTDL_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_v2_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));  // 227 KB less the static epilogue accumulators
     attr_set[dev & 63] = true;
   }
   dim3 grid(N * a.tiles_h, n_tiles);

@@ -1,0 +1,56 @@
+// Epilogue helpers shared by the implicit-GEMM kernels: per-channel sum / sum-of-squares of the
+// tile that is being written (the statistics the following training-mode BatchNorm needs),
+// taken from the fp32 accumulators after rounding to the stored bf16 value.
+#pragma once
+#include "../common/ptx.cuh"
+
+namespace dtdl {
+
+// Butterfly reduce-scatter across a warp: on return lane L holds sum over all lanes of v[L].
+// 31 shuffles for 32 values (a plain all-reduce per value would need 160).
+__device__ __forceinline__ float warp_reduce_scatter32(float (&v)[32], int lane) {
+#pragma unroll
+  for (int half = 16; half >= 1; half >>= 1) {
+    const bool upper = (lane & half) != 0;
+#pragma unroll
+    for (int j = 0; j < half; ++j) {
+      const float send = upper ? v[j] : v[j + half];
+      const float keep = upper ? v[j + half] : v[j];
+      v[j] = keep + __shfl_xor_sync(0xffffffffu, send, half);
+    }
+  }
+  return v[0];
+}
+
+// One 16-column chunk of one warp's 32 rows -> shared accumulators s_sums[2][n_tile].
+__device__ __forceinline__ void epilogue_col_stats(const float (&f)[16], bool valid, int lane,
+                                                   float* s_sums, int n_tile, int jcol) {
+  float v[32];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const float x = valid ? __bfloat162float(__float2bfloat16(f[i])) : 0.f;
+    v[i] = x;
+    v[16 + i] = x * x;
+  }
+  const float tot = warp_reduce_scatter32(v, lane);
+  atomicAdd(&s_sums[(lane < 16 ? 0 : n_tile) + jcol + (lane & 15)], tot);
+}
+
+// named barrier over the 128 epilogue threads (id 1; id 0 is __syncthreads)
+__device__ __forceinline__ void epilogue_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+__device__ __forceinline__ void epilogue_stats_init(float* s_sums, int n_tile, int etid) {
+  for (int t = etid; t < 2 * n_tile; t += 128) s_sums[t] = 0.f;
+  epilogue_bar();
+}
+
+__device__ __forceinline__ void epilogue_stats_flush(const float* s_sums, float* stats, int n_tile,
+                                                     int col_base, int Cout_p, int etid) {
+  epilogue_bar();
+  for (int t = etid; t < 2 * n_tile; t += 128) {
+    const int col = col_base + (t % n_tile);
+    if (col < Cout_p) atomicAdd(stats + (t < n_tile ? 0 : Cout_p) + col, s_sums[t]);
+  }
+}
+
+}  // namespace dtdl

@@ -44,8 +44,8 @@ class PyramidBlock(nn.Module):
 
     def forward(self, x):
         shortcut = x if self.pool is None else self.pool(x)
-        out = self.conv1(self.bn1(x))
-        out = self.conv2(self.bn2(out, relu=True))
+        out = self.conv1(self.bn1(x), stats_for=self.bn2)
+        out = self.conv2(self.bn2(out, relu=True), stats_for=self.bn3)
         # bn3 + shortcut on the first cin channels == out += F.pad(shortcut)
         return self.bn3(out, residual=shortcut)
 
@@ -81,7 +81,7 @@ class PyramidNet(nn.Module):
                 nn.init.constant_(m.bias, 0)
 
     def forward(self, x):
-        x = self.bn1(self.conv1(self.input(x)))
+        x = self.bn1(self.conv1(self.input(x), stats_for=self.bn1))
         x = self.layer3(self.layer2(self.layer1(x)))
         x = self.avgpool(self.bn_out(x, relu=True))
         if not x.is_cuda:

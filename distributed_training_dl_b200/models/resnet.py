@@ -123,10 +123,15 @@ class Bottleneck(nn.Module):
             self.downsample = nn.Sequential(L.Conv2d(cin, cout, 1, stride=stride, bias=False), L.BatchNorm2d(cout))
 
     def forward(self, x):
-        identity = x if self.downsample is None else self.downsample(x)
-        out = self.bn1(self.conv1(x), relu=True)
-        out = self.bn2(self.conv2(out), relu=True)
-        return self.bn3(self.conv3(out), residual=identity, relu=True)   # relu(bn3 + identity)
+        # every stride-1 GEMM also sums its output for the BatchNorm that follows (stats_for)
+        if self.downsample is None:
+            identity = x
+        else:
+            ds_conv, ds_bn = self.downsample
+            identity = ds_bn(ds_conv(x, stats_for=ds_bn))
+        out = self.bn1(self.conv1(x, stats_for=self.bn1), relu=True)
+        out = self.bn2(self.conv2(out, stats_for=self.bn2), relu=True)
+        return self.bn3(self.conv3(out, stats_for=self.bn3), residual=identity, relu=True)   # relu(bn3 + identity)
 
 
 class ResNet50(nn.Module):

@@ -8,10 +8,15 @@ so autograd never materialises or accumulates a weight gradient itself.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from .. import _native as nv
 
+
+# DTDL_FUSE_BN_STATS=0 keeps the separate statistics pass (A/B measurements)
+FUSE_BN_STATS = os.environ.get("DTDL_FUSE_BN_STATS", "1") != "0"
 
 def pad8(c: int) -> int:
     return (c + 7) // 8 * 8
@@ -144,15 +149,29 @@ def _conv_out(n, k, pad):
     return n + 2 * pad - k + 1
 
 
-def conv_fprop_raw(x, wpack, Cout_p, KH, KW, pad, bias=None, relu=False, out_f32=False, out_hw=None):
+def conv_fprop_raw(x, wpack, Cout_p, KH, KW, pad, bias=None, relu=False, out_f32=False, out_hw=None,
+                   stats=0):
+    """``stats``: device address of a zeroed fp32 [2*Cout_p] buffer that receives the per-channel
+    sum / sum of squares of the output (the following BatchNorm's batch statistics)."""
     N, H, W, Cin_p = x.shape
     Ho, Wo = out_hw or (_conv_out(H, KH, pad), _conv_out(W, KW, pad))
     y = torch.empty((N, Ho, Wo, Cout_p), dtype=torch.float32 if out_f32 else torch.bfloat16,
                     device=x.device)
     flags = (1 if relu else 0) | (2 if out_f32 else 0)
-    nv.call("conv_fprop", nv.ptr(x), nv.ptr(wpack), nv.ptr(y), nv.ptr(bias), N, H, W, Cin_p, Ho, Wo,
-            Cout_p, KH, KW, pad, pad, flags, nv.stream_ptr())
+    nv.call("conv_fprop_stats", nv.ptr(x), nv.ptr(wpack), nv.ptr(y), nv.ptr(bias), stats, N, H, W,
+            Cin_p, Ho, Wo, Cout_p, KH, KW, pad, pad, flags, nv.stream_ptr())
     return y
+
+
+def _claim_bn_stats(bn, device, Cp):
+    """Hand the BatchNorm's statistics buffer to the producer of its input: returns the address
+    the producer accumulates into, and marks the module so its forward skips the stats pass."""
+    stat = bn._stat_buffer(device, Cp)
+    if bn._fwd_dirty:
+        stat[: 2 * Cp].zero_()
+    bn._fwd_dirty = True
+    bn._stats_from_producer = True
+    return stat.data_ptr()
 
 
 def subsample2_raw(x, adjoint=False, full_hw=None):
@@ -176,10 +195,15 @@ class _Conv(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, x, weight, bias, mod):
+    def forward(ctx, x, weight, bias, mod, stats_for=None):
         x = x.contiguous()
+        stats = 0
+        if (stats_for is not None and mod.conv_stride == 1 and FUSE_BN_STATS
+                and (stats_for.training or stats_for.running_mean is None)):
+            stats = _claim_bn_stats(stats_for, x.device, mod.Cout_p)
         y = conv_fprop_raw(x, mod.wf, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad, bias=bias,
-                           relu=mod.fuse_relu, out_f32=False, out_hw=getattr(mod, "out_hw", None))
+                           relu=mod.fuse_relu, out_f32=False, out_hw=getattr(mod, "out_hw", None),
+                           stats=stats)
         full_hw = (y.shape[1], y.shape[2])
         if mod.conv_stride == 2:
             y = subsample2_raw(y)
@@ -227,11 +251,13 @@ class _Conv(torch.autograd.Function):
         dx = None
         if ctx.needs_input_grad[0]:
             dx = conv_fprop_raw(dy, mod.wd, Cin_p, mod.KH, mod.KW, mod.KH - 1 - mod.conv_pad)
-        return dx, (gw if returned else None), None, None
+        return dx, (gw if returned else None), None, None, None
 
 
-def conv(x, mod):
-    return _Conv.apply(x, mod.weight, mod.bias, mod)
+def conv(x, mod, stats_for=None):
+    """``stats_for``: the training-mode BatchNorm2d that consumes this convolution's output; its
+    batch statistics then come out of the GEMM epilogue (stride-1 convolutions only)."""
+    return _Conv.apply(x, mod.weight, mod.bias, mod, stats_for)
 
 
 class _Subsample(torch.autograd.Function):
@@ -282,7 +308,9 @@ class _BatchNorm(torch.autograd.Function):
         if residual is not None:
             residual = residual.contiguous()
         Cres_p = residual.shape[-1] if residual is not None else 0
-        if training:
+        if training and getattr(mod, "_stats_from_producer", False):
+            mod._stats_from_producer = False  # the kernel that wrote x already summed it
+        elif training:
             if mod._fwd_dirty:
                 stat[: 2 * Cp].zero_()
             nv.call("bn_stats", nv.ptr(x), nv.ptr(stat), P, Cp, st)

@@ -107,14 +107,15 @@ class Conv2d(nn.Conv2d, _PackedWeightMixin):
         self.fuse_relu = activation == "relu"
         assert activation in (None, "relu")
 
-    def forward(self, x):
+    def forward(self, x, stats_for=None):
+        """``stats_for``: the BatchNorm2d applied next to the result (see fn.conv)."""
         if not is_native(x):
             y = super().forward(x)
             return F.relu(y) if self.fuse_relu else y
         self._ensure_packed()
         if self.pre_subsample:
             x = fn.subsample2(x)
-        return fn.conv(x, self)
+        return fn.conv(x, self, stats_for=stats_for)
 
 
 class Linear(nn.Linear, _PackedWeightMixin):
@@ -145,6 +146,7 @@ class BatchNorm2d(nn.BatchNorm2d):
         super().__init__(num_features, eps=eps, momentum=momentum)
         self._stat = None
         self._fwd_dirty = False
+        self._stats_from_producer = False   # set by the kernel that sums our input for us
 
     def _stat_buffer(self, device, Cp):
         if self._stat is None or self._stat.device != device or self._stat.numel() != 4 * Cp:

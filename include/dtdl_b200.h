@@ -33,6 +33,13 @@ int dtdl_conv_fprop(const void* x, const void* wpack, void* y, const float* bias
                     int W, int Cin_p, int Ho, int Wo, int Cout_p, int KH, int KW, int pad_h,
                     int pad_w, int flags, void* stream);
 
+/* Same, and additionally accumulates the per-channel sum / sum of squares of the stored output
+ * into stats[2*Cout_p] (pre-zeroed): the batch statistics of the BatchNorm that follows the
+ * convolution (pytorch/model.py:41-46) come out of the GEMM epilogue instead of a separate pass. */
+int dtdl_conv_fprop_stats(const void* x, const void* wpack, void* y, const float* bias, float* stats,
+                          int N, int H, int W, int Cin_p, int Ho, int Wo, int Cout_p, int KH, int KW,
+                          int pad_h, int pad_w, int flags, void* stream);
+
 /* Weight gradient (autograd of the layers above; pytorch/single_gpu.py:102).  Writes (or
  * accumulates into) the fp32 OIHW gradient `dw`.  Needs scratch of the size returned by
  * dtdl_conv_wgrad_workspace_bytes for the same shape. */

@@ -66,6 +66,38 @@ def test_conv_forward_backward(case):
     assert _rel_err(conv.weight.grad, ref_w.grad) < 1e-2
 
 
+@pytest.mark.parametrize("case", [(4, 21, 26, 32, 32, 3, 1), (8, 266, 271, 8, 8, 3, 1), (4, 32, 64, 13, 13, 3, 0),
+                                  (2, 64, 256, 14, 14, 1, 0), (2, 64, 64, 56, 56, 3, 1), (16, 16, 16, 32, 32, 3, 1)])
+def test_conv_epilogue_bn_statistics(case):
+    """conv(x, stats_for=bn) + bn == conv + bn with its own statistics pass, and both == fp32
+    torch; two steps in a row so the re-zeroing of the shared buffer is covered."""
+    from distributed_training_dl_b200.ops import BatchNorm2d, Conv2d, functional as fn
+    N, Cin, Cout, H, W, k, pad = case
+    torch.manual_seed(1)
+    conv = Conv2d(Cin, Cout, k, padding=pad, bias=False).cuda()
+    with torch.no_grad():
+        conv.weight.copy_(_bf(conv.weight))
+    bn_a, bn_b, ref = BatchNorm2d(Cout).cuda(), BatchNorm2d(Cout).cuda(), torch.nn.BatchNorm2d(Cout).cuda()
+    for step in range(2):
+        x = _bf(torch.randn(N, Cin, H, W, device="cuda") + 0.3 * step)
+        xn = fn.to_nhwc(x).requires_grad_(True)
+        ya = bn_a(conv(xn, stats_for=bn_a), relu=True)
+        assert not bn_a._stats_from_producer          # consumed by the BatchNorm
+        yb = bn_b(conv(xn), relu=True)
+        ry = F.relu(ref(_bf(F.conv2d(x, conv.weight, padding=pad))))
+        assert _rel_err(ya.float(), yb.float()) < 1e-2
+        assert _rel_err(_nhwc_to_nchw(ya, Cout), ry) < 2e-2
+        assert torch.allclose(bn_a.running_mean, bn_b.running_mean, atol=1e-4)
+        assert torch.allclose(bn_a.running_var, bn_b.running_var, rtol=1e-3, atol=1e-4)
+        assert torch.allclose(bn_a.running_var, ref.running_var, rtol=1e-2, atol=1e-3)
+        dy = fn.to_nhwc(_bf(torch.randn_like(ry)))
+        ya.backward(dy)
+        ga = xn.grad.clone()
+        xn.grad = None
+        yb.backward(dy)
+        assert _rel_err(ga.float(), xn.grad.float()) < 1e-2
+
+
 @pytest.mark.parametrize("N,Fin,Fout", [(64, 784, 1000), (100, 1000, 10), (7, 271, 10), (256, 576, 64)])
 def test_linear_forward_backward(N, Fin, Fout):
     from distributed_training_dl_b200.ops import Linear, functional as fn
