@@ -63,6 +63,12 @@ def main():
                                   comm, iters)
         res["fused-sgd"] = time_op(lambda: peer.reduce_update(src, params, m, None, hyper, 0, n, 1, two_shot=1,
                                                               max_blocks=args.blocks), comm, iters)
+        if peer.use_nvls and src.mc_ptr:     # DTDL_NVLS=1: in-switch reduction through the multicast address
+            res["nvls"] = time_op(lambda: peer.allreduce(src, 0, n, two_shot=2, dst=dst, max_blocks=args.blocks),
+                                  comm, iters)
+            res["nvls-fused-sgd"] = time_op(lambda: peer.reduce_update(src, params, m, None, hyper, 0, n, 1,
+                                                                       two_shot=2, max_blocks=args.blocks),
+                                            comm, iters)
         if nccl is not None:
             x = t[:n]
             res["nccl"] = time_op(lambda: dist.all_reduce(x, group=nccl), comm, iters)

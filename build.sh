@@ -8,13 +8,13 @@ NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS=(-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC
        -Xptxas -v --expt-relaxed-constexpr -Iinclude)
 SRCS=(csrc/common/host.cpp csrc/common/api.cpp csrc/ops/conv_gemm.cu csrc/ops/conv_gemm_v2.cu csrc/ops/conv_wgrad.cu
-      csrc/ops/nn_ops.cu csrc/ops/pack.cu csrc/comm/collectives.cu)
+      csrc/ops/nn_ops.cu csrc/ops/pack.cu csrc/comm/collectives.cu csrc/comm/vmm.cpp)
 OBJS=()
 pids=()
 for s in "${SRCS[@]}"; do
   o=build/$(echo "$s" | tr '/' '_').o
   OBJS+=("$o")
-  if [[ ! -f "$o" || "$s" -nt "$o" || csrc/common/ptx.cuh -nt "$o" || csrc/common/host.h -nt "$o" || include/dtdl_b200.h -nt "$o" ]]; then
+  if [[ ! -f "$o" || "$s" -nt "$o" || csrc/common/ptx.cuh -nt "$o" || csrc/common/host.h -nt "$o" || csrc/ops/epilogue.cuh -nt "$o" || include/dtdl_b200.h -nt "$o" ]]; then
     ( "$NVCC" "${FLAGS[@]}" -x cu -c "$s" -o "$o" > "build/$(basename "$o").log" 2>&1 || { cat "build/$(basename "$o").log"; exit 1; } ) &
     pids+=($!)
   fi

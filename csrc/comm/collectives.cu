@@ -12,6 +12,11 @@
 //   two-shot : rank r reduces slice r from all W copies, then stores the
 //              result into all W destinations (bandwidth optimal on NVSwitch)
 //
+//   multicast: (NVLS, buffers from the vmm.cpp allocator) rank r reads slice r through the
+//              multicast address with multimem.ld_reduce -- NVSwitch sums the W copies and
+//              returns one value -- and writes the result with multimem.st, which the switch
+//              replicates to all W ranks: 1/W of the NVLink traffic of two-shot per GPU
+//
 // The fused variants apply cast + 1/W + weight decay + SGD-momentum or Adam to
 // the reduced gradient and (two-shot) scatter the *updated parameters* instead
 // of gradients, so gradient all-reduce, averaging and optimizer.step() are one
@@ -147,12 +152,12 @@ struct ReduceArgs {
   int opt;           // OPT_*
   int two_shot;
   float scale;       // plain all-reduce: multiply the sum by this (1 or 1/W)
+  const float* mc_grads;  // multicast variant: multicast address of the gradient bucket
+  float* mc_dst;          //                    multicast address of the destination bucket
 };
 
 // Applies the epilogue (scale, or optimizer update) to one reduced 4-vector and stores it.
-template <int WT>
-__device__ __forceinline__ void reduce_finish(const CommDev& c, const ReduceArgs& a, int W,
-                                              long long i, float4 s) {
+__device__ __forceinline__ float4 reduce_epilogue(const ReduceArgs& a, long long i, float4 s) {
   float4 out;
   if (a.opt == OPT_NONE) {
     out = make_float4(s.x * a.scale, s.y * a.scale, s.z * a.scale, s.w * a.scale);
@@ -176,6 +181,13 @@ __device__ __forceinline__ void reduce_finish(const CommDev& c, const ReduceArgs
     reinterpret_cast<float4*>(a.mom)[i] = m;
     out = p;
   }
+  return out;
+}
+
+template <int WT>
+__device__ __forceinline__ void reduce_finish(const CommDev& c, const ReduceArgs& a, int W,
+                                              long long i, float4 s) {
+  const float4 out = reduce_epilogue(a, i, s);
   if (a.two_shot && W > 1) {
 #pragma unroll
     for (int r = 0; r < (WT ? WT : kMaxWorld); ++r)
@@ -242,6 +254,67 @@ static void launch_reduce(const CommDev& d, const ReduceArgs& a, int grid, cudaS
     case 8: reduce_kernel<8><<<grid, 512, 0, stream>>>(d, a); break;
     default: reduce_kernel<0><<<grid, 512, 0, stream>>>(d, a); break;
   }
+}
+
+// ---- NVLS (multicast) variants ---------------------------------------------------------------
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x),
+               "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+// Rank r owns slice r: one in-switch reduction per 16 bytes in, one replicated store out.  The
+// slice's parameters / optimizer state are read and written locally, as in two-shot.  The order
+// in which the switch adds the W values is fixed by the hardware, not by rank; results are
+// still identical on every rank because every rank receives the same stored value.
+__global__ void __launch_bounds__(512)
+nvls_reduce_kernel(const CommDev c, const ReduceArgs a) {
+  constexpr int kUnroll = 4;
+  const uint32_t e = *c.epoch + 1;
+  comm_start(c, e);
+  const int W = c.world;
+  const long long n4 = a.n / 4;
+  const long long per = (n4 + W - 1) / W;
+  long long begin4 = per * c.rank;
+  const long long end4 = begin4 + per < n4 ? begin4 + per : n4;
+  if (begin4 > end4) begin4 = end4;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = begin4 + blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < end4;
+       i0 += stride * kUnroll) {
+    float4 s[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < end4) s[u] = multimem_ld_reduce_f4(a.mc_grads + 4 * i);
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < end4) multimem_st_f4(a.mc_dst + 4 * i, reduce_epilogue(a, i, s[u]));
+    }
+  }
+  comm_finish(c, e);
+}
+
+// The root pushes its copy once; the switch delivers it to every rank (the root included).
+__global__ void __launch_bounds__(512)
+nvls_broadcast_kernel(const CommDev c, const float* local, float* mc, long long n16, int root) {
+  const uint32_t e = *c.epoch + 1;
+  comm_start(c, e);
+  if (c.rank == root) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += stride)
+      multimem_st_f4(mc + 4 * i, reinterpret_cast<const float4*>(local)[i]);
+  }
+  comm_finish(c, e);
 }
 
 // Every non-root rank pulls `n16` 16-byte words from the root's copy.
@@ -514,6 +587,70 @@ extern "C" int dtdl_local_update(float* param, const float* grad, float* mom, fl
   if (g > 148 * 4) g = 148 * 4;
   if (g < 1) g = 1;
   local_update_kernel<<<(int)g, 512, 0, STREAM(stream)>>>(param, grad, mom, var, hyper, n / 4, opt);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ---- NVLS entry points: `mc_*` are multicast addresses of buffers from dtdl_vmm_* / dtdl_mc_* ----
+extern "C" int dtdl_comm_nvls_allreduce(void* handle, void* mc_src, void* mc_dst, long long offset_bytes,
+                                        long long n, float scale, int max_blocks, void* stream) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  DTDL_REQUIRE(n % 4 == 0 && offset_bytes % 16 == 0, "buckets must be 16-byte granular");
+  DTDL_REQUIRE(mc_src != nullptr && mc_dst != nullptr, "buffer has no multicast mapping");
+  ReduceArgs a;
+  memset(&a, 0, sizeof(a));
+  a.mc_grads = reinterpret_cast<const float*>(reinterpret_cast<char*>(mc_src) + offset_bytes);
+  a.mc_dst = reinterpret_cast<float*>(reinterpret_cast<char*>(mc_dst) + offset_bytes);
+  a.n = n;
+  a.opt = OPT_NONE;
+  a.two_shot = 1;
+  a.scale = scale;
+  const int grid = comm_grid(n / 4, h->d.world, 1, max_blocks > 0 ? max_blocks : 64);
+  nvls_reduce_kernel<<<grid, 512, 0, STREAM(stream)>>>(h->d, a);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_comm_nvls_reduce_update(void* handle, void* mc_grads, void* mc_params, float* param,
+                                            float* mom, float* var, const float* hyper,
+                                            long long offset_bytes, long long n, int opt, int max_blocks,
+                                            void* stream) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  DTDL_REQUIRE(n % 4 == 0 && offset_bytes % 16 == 0, "buckets must be 16-byte granular");
+  DTDL_REQUIRE(opt == OPT_SGD || opt == OPT_ADAM || opt == OPT_ADAM_KERAS, "unknown optimizer");
+  DTDL_REQUIRE(mc_grads != nullptr && mc_params != nullptr, "buffer has no multicast mapping");
+  ReduceArgs a;
+  memset(&a, 0, sizeof(a));
+  a.mc_grads = reinterpret_cast<const float*>(reinterpret_cast<char*>(mc_grads) + offset_bytes);
+  a.mc_dst = reinterpret_cast<float*>(reinterpret_cast<char*>(mc_params) + offset_bytes);
+  a.param = reinterpret_cast<float*>(reinterpret_cast<char*>(param) + offset_bytes);
+  a.mom = reinterpret_cast<float*>(reinterpret_cast<char*>(mom) + offset_bytes);
+  a.var = var ? reinterpret_cast<float*>(reinterpret_cast<char*>(var) + offset_bytes) : nullptr;
+  DTDL_REQUIRE(opt == OPT_SGD || a.var != nullptr, "Adam needs the second-moment arena");
+  a.hyper = hyper;
+  a.n = n;
+  a.opt = opt;
+  a.two_shot = 1;
+  a.scale = 1.f;
+  const int grid = comm_grid(n / 4, h->d.world, 1, max_blocks > 0 ? max_blocks : 64);
+  nvls_reduce_kernel<<<grid, 512, 0, STREAM(stream)>>>(h->d, a);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_comm_nvls_broadcast(void* handle, void* local, void* mc, long long offset_bytes,
+                                        long long bytes, int root, int max_blocks, void* stream) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  DTDL_REQUIRE(bytes % 16 == 0 && offset_bytes % 16 == 0, "buffers must be 16-byte granular");
+  DTDL_REQUIRE(local != nullptr && mc != nullptr, "buffer has no multicast mapping");
+  const long long n16 = bytes / 16;
+  long long g = (n16 + 2047) / 2048;
+  const int cap = max_blocks > 0 ? max_blocks : 64;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  nvls_broadcast_kernel<<<(int)g, 512, 0, STREAM(stream)>>>(
+      h->d, reinterpret_cast<const float*>(reinterpret_cast<char*>(local) + offset_bytes),
+      reinterpret_cast<float*>(reinterpret_cast<char*>(mc) + offset_bytes), n16, root);
   DTDL_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

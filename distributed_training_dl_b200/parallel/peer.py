@@ -11,10 +11,21 @@ One :class:`PeerComm` per GPU.  Two ways to build a group:
 
 A symmetric buffer is a :class:`SymmBuffer`: the local memory as a torch tensor plus the
 table of every rank's base pointer that the kernels dereference over NVLink.
+
+NVLS (``DTDL_NVLS=1`` or ``PeerComm.use_nvls = True`` before the first ``alloc``): buffers come
+from the cuMem allocator of csrc/comm/vmm.cpp instead, are additionally bound to an NVSwitch
+multicast object, and all-reduce / fused reduce+update / broadcast go through the multicast
+address (``multimem.ld_reduce`` / ``multimem.st``).  Handles cross processes as POSIX file
+descriptors over Unix sockets (:class:`FdChannel`).
 """
 from __future__ import annotations
 
 import ctypes
+import os
+import shutil
+import socket
+import struct
+import tempfile
 
 import torch
 
@@ -37,13 +48,69 @@ def tensor_from_ptr(ptr: int, nbytes: int, device: torch.device, owner=None) -> 
     return t
 
 
+class FdChannel:
+    """All-gather of file descriptors between the processes of one node (SCM_RIGHTS).
+
+    Every rank listens on a Unix socket whose path it publishes in the rendezvous store; an
+    exchange is "send my fds to every peer, then accept one message from every peer".  A sent
+    message waits in the listener's queue until it is accepted, so no rank blocks another.
+    """
+
+    def __init__(self, rank: int, world: int, store, barrier):
+        self.rank, self.world, self._barrier = rank, world, barrier
+        self._dir = tempfile.mkdtemp(prefix="dtdl_fd_")
+        path = os.path.join(self._dir, f"rank{rank}.sock")
+        self._sock = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        self._sock.bind(path)
+        self._sock.listen(4 * world)
+        store.set(f"dtdl/fdsock/{rank}", path)
+        self._paths = [store.get(f"dtdl/fdsock/{r}").decode() for r in range(world)]
+        self._seq = 0
+        barrier()
+
+    def allgather(self, fds) -> list:
+        """Every rank contributes a (possibly empty) list of fds; returns the list per rank.
+        Received descriptors are new numbers in this process and are the caller's to close."""
+        self._seq += 1
+        out = [None] * self.world
+        out[self.rank] = list(fds)
+        conns = []
+        for r in range(self.world):
+            if r == self.rank:
+                continue
+            c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            c.connect(self._paths[r])
+            socket.send_fds(c, [struct.pack("iii", self.rank, self._seq, len(fds))], list(fds))
+            conns.append(c)
+        for _ in range(self.world - 1):
+            c, _addr = self._sock.accept()
+            msg, rfds, _flags, _a = socket.recv_fds(c, 12, 16)
+            src, seq, n = struct.unpack("iii", msg)
+            if seq != self._seq or n != len(rfds):
+                raise RuntimeError(f"fd exchange out of step: rank {src} sent seq {seq} ({len(rfds)}/{n} fds), "
+                                   f"expected seq {self._seq}")
+            out[src] = list(rfds)
+            c.close()
+        self._barrier()       # nobody starts the next exchange before this one is drained
+        for c in conns:
+            c.close()
+        return out
+
+    def close(self):
+        self._sock.close()
+        shutil.rmtree(self._dir, ignore_errors=True)
+
+
 class SymmBuffer:
     """Same-sized allocation on every rank + the per-rank base pointer table."""
 
-    def __init__(self, comm: "PeerComm", nbytes: int, local_ptr: int, peer_ptrs, opened):
+    def __init__(self, comm: "PeerComm", nbytes: int, local_ptr: int, peer_ptrs, opened, mc_ptr: int = 0,
+                 vmm=None):
         self.comm, self.nbytes, self.local_ptr = comm, nbytes, local_ptr
         self.peer_ptrs = list(peer_ptrs)
         self._opened = opened  # IPC mappings to close
+        self.mc_ptr = mc_ptr   # NVLS multicast address of the same bytes on every rank (0: none)
+        self._vmm = vmm        # (mapped size, [mapped pointers], [handles]) of a cuMem-backed buffer
         self.ptr_array = (ctypes.c_void_p * len(self.peer_ptrs))(*self.peer_ptrs)
         self.bytes = tensor_from_ptr(local_ptr, nbytes, comm.device, owner=self)
         self._freed = False
@@ -57,6 +124,13 @@ class SymmBuffer:
         if self._freed:
             return
         self._freed = True
+        if self._vmm is not None:
+            size, ptrs, handles = self._vmm
+            for p in ptrs:
+                nv.lib().dtdl_vmm_unmap(ctypes.c_void_p(p), size)
+            for h in handles:
+                nv.lib().dtdl_vmm_release(h)
+            return
         with torch.cuda.device(self.comm.device):
             for p in self._opened:
                 nv.lib().dtdl_ipc_close_handle(p)
@@ -76,6 +150,10 @@ class PeerComm:
         self._buffers = []
         self.max_blocks = 32        # SM budget of a collective kernel (leaves SMs to backward)
         self.two_shot_min_bytes = 256 * 1024
+        # NVLS: allocate through cuMem + multicast and reduce inside NVSwitch
+        self.use_nvls = world > 1 and os.environ.get("DTDL_NVLS", "0") == "1"
+        self.nvls_min_bytes = int(os.environ.get("DTDL_NVLS_MIN_BYTES", "0"))
+        self._fdchan = None
 
     # ------------------------------------------------------------------ construction
     @classmethod
@@ -130,11 +208,73 @@ class PeerComm:
         dist.barrier(group=self._control)
         return ptrs
 
+    # ------------------------------------------------------------------ cuMem / multicast plumbing
+    def _vmm_size(self, nbytes: int):
+        gran = nv.lib().dtdl_vmm_granularity(self.device.index or 0, self.world)
+        if gran <= 0:
+            raise nv.NativeError("cuMem / multicast granularity query failed: NVLS is not available here")
+        return (nbytes + gran - 1) // gran * gran, gran
+
+    def _alloc_vmm(self, nbytes: int) -> SymmBuffer:
+        """cuMem-backed symmetric buffer with peer mappings and a multicast mapping (multi-process)."""
+        import torch.distributed as dist
+        dev = self.device.index or 0
+        size, gran = self._vmm_size(nbytes)
+        if self._fdchan is None:
+            self._fdchan = FdChannel(self.rank, self.world, self._store,
+                                     lambda: dist.barrier(group=self._control))
+        ll, ci = ctypes.c_longlong, ctypes.c_int
+        mem = ll()
+        nv.call("vmm_create", dev, size, 1, ctypes.byref(mem))
+        fd = ci()
+        nv.call("vmm_export_fd", mem, ctypes.byref(fd))
+        mine = [fd.value]
+        mc = ll()
+        if self.rank == 0:
+            nv.call("mc_create", self.world, size, 1, ctypes.byref(mc))
+            nv.call("vmm_export_fd", mc, ctypes.byref(fd))
+            mine.append(fd.value)
+        gathered = self._fdchan.allgather(mine)
+        devs = (ci * 1)(dev)
+        ptrs, mapped = [], []
+        for r in range(self.world):
+            h = mem
+            if r != self.rank:
+                h = ll()
+                nv.call("vmm_import_fd", gathered[r][0], ctypes.byref(h))
+            out = ctypes.c_void_p()
+            nv.call("vmm_map", h, size, gran, devs, 1, ctypes.byref(out))
+            if r != self.rank:
+                nv.call("vmm_release", h)      # the mapping keeps the peer's memory alive
+            ptrs.append(int(out.value))
+            mapped.append(int(out.value))
+        if self.rank != 0:
+            nv.call("vmm_import_fd", gathered[0][1], ctypes.byref(mc))
+        nv.call("mc_add_device", mc, dev)
+        dist.barrier(group=self._control)      # binding needs the whole team added
+        nv.call("mc_bind", mc, mem, size)
+        out = ctypes.c_void_p()
+        nv.call("vmm_map", mc, size, gran, devs, 1, ctypes.byref(out))
+        mapped.append(int(out.value))
+        for fds in gathered:
+            for f in fds:
+                os.close(f)
+        buf = SymmBuffer(self, nbytes, ptrs[self.rank], ptrs, [], mc_ptr=int(out.value),
+                         vmm=(size, mapped, [mem, mc]))
+        buf.bytes.zero_()
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self._control)
+        return buf
+
     def alloc(self, nbytes: int, tag: str = "buf") -> SymmBuffer:
         """Collective: every rank must call with the same size in the same order."""
         nbytes = (int(nbytes) + 255) // 256 * 256
         if self._local_group is not None:
             raise RuntimeError("use PeerComm.alloc_local(comms, nbytes) in single-process mode")
+        if self.use_nvls and self.world > 1:
+            buf = self._alloc_vmm(nbytes)
+            self._buffers.append(buf)
+            return buf
         out = ctypes.c_void_p()
         with torch.cuda.device(self.device):
             nv.call("symm_alloc", nbytes, ctypes.byref(out))
@@ -149,8 +289,47 @@ class PeerComm:
         return buf
 
     @staticmethod
+    def _alloc_local_vmm(comms, nbytes: int):
+        """Single-process flavour of :meth:`_alloc_vmm`: handles are used directly, no fds."""
+        ll, ci = ctypes.c_longlong, ctypes.c_int
+        world = len(comms)
+        size, gran = comms[0]._vmm_size(nbytes)
+        idx = [c.device.index or 0 for c in comms]
+        all_devs = (ci * world)(*idx)
+        mems = []
+        for d in idx:
+            h = ll()
+            nv.call("vmm_create", d, size, 0, ctypes.byref(h))
+            mems.append(h)
+        mc = ll()
+        nv.call("mc_create", world, size, 0, ctypes.byref(mc))
+        for d in idx:
+            nv.call("mc_add_device", mc, d)
+        ptrs = []
+        for h in mems:
+            nv.call("mc_bind", mc, h, size)
+            out = ctypes.c_void_p()
+            nv.call("vmm_map", h, size, gran, all_devs, world, ctypes.byref(out))
+            ptrs.append(int(out.value))
+        bufs = []
+        for c, d in zip(comms, idx):
+            out = ctypes.c_void_p()
+            nv.call("vmm_map", mc, size, gran, (ci * 1)(d), 1, ctypes.byref(out))
+            # rank 0's buffer owns the shared mappings and handles
+            own = (size, [int(out.value)] + (ptrs if c.rank == 0 else []), (mems + [mc]) if c.rank == 0 else [])
+            b = SymmBuffer(c, nbytes, ptrs[c.rank], ptrs, [], mc_ptr=int(out.value), vmm=own)
+            b.bytes.zero_()
+            c._buffers.append(b)
+            bufs.append(b)
+        for c in comms:
+            torch.cuda.synchronize(c.device)
+        return bufs
+
+    @staticmethod
     def alloc_local(comms, nbytes: int):
         nbytes = (int(nbytes) + 255) // 256 * 256
+        if comms[0].use_nvls and len(comms) > 1:
+            return PeerComm._alloc_local_vmm(comms, nbytes)
         ptrs = []
         for c in comms:
             out = ctypes.c_void_p()
@@ -173,8 +352,17 @@ class PeerComm:
         return (stream or torch.cuda.current_stream(self.device)).cuda_stream
 
     def choose_two_shot(self, nbytes: int) -> int:
-        """One-shot below the measured crossover, two-shot above (see profiles/allreduce_sweep.md)."""
+        """One-shot (0) below the measured crossover, two-shot (1) above (see
+        profiles/allreduce_sweep.md); 2 = the multicast variant, which shards work like two-shot."""
+        if self.use_nvls and self.world > 1 and nbytes >= self.nvls_min_bytes:
+            return 2
         return 1 if (self.world > 1 and nbytes >= self.two_shot_min_bytes) else 0
+
+    def _nvls_ok(self, a: SymmBuffer, b: SymmBuffer, nbytes: int) -> bool:
+        """Multicast path possible: both buffers are bound to a multicast object and the message
+        is at least ``nvls_min_bytes``."""
+        return bool(self.use_nvls and self.world > 1 and a.mc_ptr and b.mc_ptr
+                    and nbytes >= self.nvls_min_bytes)
 
     def barrier(self, stream=None):
         nv.call("comm_barrier", self.handle, self._stream(stream))
@@ -185,10 +373,16 @@ class PeerComm:
         in_place = dst is None or dst is buf
         dst = dst or buf
         ts = self.choose_two_shot(numel * 4) if two_shot is None else int(two_shot)
-        if in_place and self.world > 1:
-            # one-shot reads every rank's whole buffer, so it may not overwrite its source;
-            # two-shot only writes the slice that nobody else reads
+        if ts == 2 and not self._nvls_ok(buf, dst, numel * 4):
             ts = 1
+        if in_place and self.world > 1 and ts == 0:
+            # one-shot reads every rank's whole buffer, so it may not overwrite its source;
+            # two-shot and multicast only write the slice that nobody else reads
+            ts = 1
+        if ts == 2:
+            nv.call("comm_nvls_allreduce", self.handle, ctypes.c_void_p(buf.mc_ptr), ctypes.c_void_p(dst.mc_ptr),
+                    offset_bytes, numel, scale, max_blocks or self.max_blocks, self._stream(stream))
+            return
         nv.call("comm_allreduce", self.handle, buf.ptr_array, dst.ptr_array, offset_bytes, numel, scale, ts,
                 max_blocks or self.max_blocks, self._stream(stream))
 
@@ -196,12 +390,23 @@ class PeerComm:
                       numel: int, opt: int, two_shot=None, stream=None, max_blocks=None):
         """Fused gradient all-reduce + 1/W + weight decay + SGD/Adam update of a bucket."""
         ts = self.choose_two_shot(numel * 4) if two_shot is None else int(two_shot)
+        if ts == 2 and not self._nvls_ok(grads, params, numel * 4):
+            ts = 1
+        if ts == 2:
+            nv.call("comm_nvls_reduce_update", self.handle, ctypes.c_void_p(grads.mc_ptr),
+                    ctypes.c_void_p(params.mc_ptr), ctypes.c_void_p(params.local_ptr), nv.ptr(mom), nv.ptr(var),
+                    nv.ptr(hyper), offset_bytes, numel, opt, max_blocks or self.max_blocks, self._stream(stream))
+            return
         nv.call("comm_reduce_update", self.handle, grads.ptr_array, params.ptr_array, nv.ptr(mom),
                 nv.ptr(var), nv.ptr(hyper), offset_bytes, numel, opt, ts, max_blocks or self.max_blocks,
                 self._stream(stream))
 
     def broadcast(self, buf: SymmBuffer, offset_bytes: int, nbytes: int, root: int = 0, stream=None,
                   max_blocks=None):
+        if self._nvls_ok(buf, buf, nbytes):
+            nv.call("comm_nvls_broadcast", self.handle, ctypes.c_void_p(buf.local_ptr), ctypes.c_void_p(buf.mc_ptr),
+                    offset_bytes, nbytes, root, max_blocks or self.max_blocks, self._stream(stream))
+            return
         nv.call("comm_broadcast", self.handle, buf.ptr_array, offset_bytes, nbytes, root,
                 max_blocks or self.max_blocks, self._stream(stream))
 
@@ -214,6 +419,9 @@ class PeerComm:
         for b in self._buffers:
             b.free()
         self._buffers = []
+        if self._fdchan is not None:
+            self._fdchan.close()
+            self._fdchan = None
         if self.handle:
             nv.lib().dtdl_comm_destroy(self.handle)
             self.handle = ctypes.c_void_p()

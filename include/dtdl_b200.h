@@ -147,6 +147,32 @@ int dtdl_comm_allgather(void* handle, void* const* bufs, long long offset_bytes,
 int dtdl_local_update(float* param, const float* grad, float* mom, float* var, const float* hyper,
                       long long n, int opt, void* stream);
 
+/* ---- NVLS: symmetric memory through cuMem* + multicast objects (csrc/comm/vmm.cpp) ----------
+ * The reference reaches NVSwitch reduction only inside NCCL (pytorch/distributed_data_parallel.py:61-62);
+ * here the buffers are allocated so that our own kernels can issue multimem.ld_reduce / multimem.st.
+ * Handles are CUmemGenericAllocationHandle values carried as long long. */
+long long dtdl_vmm_granularity(int dev, int world);
+int dtdl_vmm_create(int dev, long long bytes, int shareable, long long* handle);
+int dtdl_vmm_export_fd(long long handle, int* fd);
+int dtdl_vmm_import_fd(int fd, long long* handle);
+int dtdl_vmm_map(long long handle, long long bytes, long long align, const int* devs, int ndevs, void** ptr);
+int dtdl_vmm_unmap(void* ptr, long long bytes);
+int dtdl_vmm_release(long long handle);
+int dtdl_vmm_close_fd(int fd);
+int dtdl_mc_create(int world, long long bytes, int shareable, long long* handle);
+int dtdl_mc_add_device(long long mc, int dev);
+int dtdl_mc_bind(long long mc, long long mem, long long bytes);
+
+/* Collectives through the multicast address (two-shot shape: rank r reduces slice r in the
+ * switch and stores the result -- or the updated parameters -- to every rank at once). */
+int dtdl_comm_nvls_allreduce(void* handle, void* mc_src, void* mc_dst, long long offset_bytes, long long n,
+                             float scale, int max_blocks, void* stream);
+int dtdl_comm_nvls_reduce_update(void* handle, void* mc_grads, void* mc_params, float* param, float* mom,
+                                 float* var, const float* hyper, long long offset_bytes, long long n, int opt,
+                                 int max_blocks, void* stream);
+int dtdl_comm_nvls_broadcast(void* handle, void* local, void* mc, long long offset_bytes, long long bytes,
+                             int root, int max_blocks, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -15,18 +15,36 @@ def _ok(outdir, i):
     open(os.path.join(outdir, f"ok_{i}"), "w").write("ok")
 
 
-def collectives(i, world, outdir):
+def _nvls_or_skip(comm, outdir, i):
+    """NVLS runs need multicast support (NVSwitch + fabric manager); otherwise record a skip."""
+    if comm.peer.multicast_supported():
+        assert comm.peer.use_nvls
+        return True
+    open(os.path.join(outdir, f"skip_{i}"), "w").write("no multicast support")
+    return False
+
+
+def collectives(i, world, outdir, nvls=False):
+    if nvls:
+        os.environ["DTDL_NVLS"] = "1"
     import distributed_training_dl_b200 as dtdl
     comm = dtdl.init(backend="b200")
     peer = comm.peer
     dev = comm.device
     assert comm.rank == i and peer.world == world
+    if nvls and not _nvls_or_skip(comm, outdir, i):
+        dtdl.shutdown()
+        return
     n = 1 << 20
     buf = peer.alloc(n * 4)
     out = peer.alloc(n * 4)
     x = buf.view(torch.float32, 0, n)
     y = out.view(torch.float32, 0, n)
-    for numel, two_shot in [(256, 0), (4096, 0), (4096, 1), (n, 0), (n, 1), (n - 8, 1)]:
+    cases = [(256, 0), (4096, 0), (4096, 1), (n, 0), (n, 1), (n - 8, 1)]
+    if nvls:    # 2 = multicast variant; the others then run the peer-pointer kernels on cuMem memory
+        assert buf.mc_ptr and out.mc_ptr
+        cases = [(256, 2), (4096, 2), (n, 2), (n - 8, 2), (4096, 0), (n, 1)]
+    for numel, two_shot in cases:
         for rep in range(3):   # repeated iterations: cross-GPU races show up as flaky mismatches
             g = torch.Generator(device="cpu").manual_seed(100 * rep + numel)
             full = torch.randn(world, numel, generator=g)
@@ -36,14 +54,14 @@ def collectives(i, world, outdir):
             torch.cuda.synchronize()
             want = full.sum(0) / world
             assert torch.allclose(y[:numel].cpu(), want, atol=1e-5), (numel, two_shot, rep)
-            # in place (always runs the two-shot schedule: one-shot may not overwrite its source)
-            peer.allreduce(buf, 0, numel, scale=1.0)
+            # in place (never the one-shot schedule: one-shot may not overwrite its source)
+            peer.allreduce(buf, 0, numel, scale=1.0, two_shot=two_shot)
             torch.cuda.synchronize()
             assert torch.allclose(x[:numel].cpu(), full.sum(0), atol=1e-5), ("inplace", numel, two_shot)
             comm.barrier()
     # bit-identical results on every rank (fixed reduction order)
     x.copy_(torch.randn(n, generator=torch.Generator().manual_seed(i)))
-    peer.allreduce(buf, 0, n, two_shot=1)
+    peer.allreduce(buf, 0, n, two_shot=2 if nvls else 1)
     torch.cuda.synchronize()
     sums = comm.allgather_object(x[:4096].cpu())
     assert all(torch.equal(sums[0], s) for s in sums)
@@ -60,7 +78,7 @@ def collectives(i, world, outdir):
     for r in range(world):
         assert float(x[r * per]) == r + 1 and float(x[(r + 1) * per - 1]) == r + 1
     # fused all-reduce + SGD / Adam against the unfused torch arithmetic
-    for opt_code, two_shot in [(1, 0), (1, 1), (2, 1), (3, 0)]:
+    for opt_code, two_shot in ([(1, 2), (2, 2), (3, 2), (1, 0)] if nvls else [(1, 0), (1, 1), (2, 1), (3, 0)]):
         numel = 1 << 16
         g = torch.Generator().manual_seed(7 + opt_code)
         grads = torch.randn(world, numel, generator=g)
@@ -94,12 +112,17 @@ def collectives(i, world, outdir):
     dtdl.shutdown()
 
 
-def ddp_training(i, world, outdir, use_graph):
+def ddp_training(i, world, outdir, use_graph, nvls=False):
+    if nvls:
+        os.environ["DTDL_NVLS"] = "1"
     import distributed_training_dl_b200 as dtdl
     from distributed_training_dl_b200.engine import CrossEntropyLoss, TrainStep
     from distributed_training_dl_b200.models import MLP, PyramidNet
     comm = dtdl.init(backend="b200")
     dev = comm.device
+    if nvls and not _nvls_or_skip(comm, outdir, i):
+        dtdl.shutdown()
+        return
     torch.manual_seed(1 + i)
     # (a) replicas identical after construction although seeded differently
     net = dtdl.wrap(PyramidNet(num_layers=3, alpha=45.0).to(dev))

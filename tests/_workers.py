@@ -112,3 +112,31 @@ def ddp_pyramidnet(i, world, port, outdir):
     rm = comm.allgather_object(net.module.bn1.running_mean.clone())
     open(os.path.join(outdir, f"ok_{i}"), "w").write("ok")
     dtdl.shutdown()
+
+
+def fd_channel(i, world, port, outdir):
+    """FdChannel (parallel/peer.py): descriptors cross processes and still name the same file."""
+    import tempfile
+    import distributed_training_dl_b200 as dtdl
+    from distributed_training_dl_b200.parallel.peer import FdChannel
+    comm = dtdl.init(backend="gloo", init_method=f"tcp://127.0.0.1:{port}", rank=i, world_size=world)
+    store = dist.distributed_c10d._get_default_store()
+    chan = FdChannel(i, world, store, lambda: dist.barrier())
+    for rnd in range(3):          # repeated exchanges must not mix
+        files = []
+        for k in range(1 + (i == 0)):     # rank 0 sends two descriptors, the others one
+            f = tempfile.TemporaryFile()
+            f.write(f"rank{i}-round{rnd}-fd{k}".encode())
+            f.flush()
+            files.append(f)
+        got = chan.allgather([f.fileno() for f in files])
+        assert len(got) == world
+        for r in range(world):
+            assert len(got[r]) == 1 + (r == 0)
+            for k, fd in enumerate(got[r]):
+                assert os.pread(fd, 64, 0).decode() == f"rank{r}-round{rnd}-fd{k}"
+                if r != i:
+                    os.close(fd)
+    chan.close()
+    open(os.path.join(outdir, f"ok_{i}"), "w").write("ok")
+    dtdl.shutdown()

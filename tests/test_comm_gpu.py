@@ -24,6 +24,26 @@ def test_peer_collectives(tmp_path):
     assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
 
 
+def _done_or_skipped(tmp_path, world):
+    if all(os.path.exists(tmp_path / f"skip_{i}") for i in range(world)):
+        pytest.skip("this box has no NVLS multicast support")
+    assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
+
+
+def test_nvls_collectives(tmp_path):
+    """multimem.ld_reduce / multimem.st all-reduce, fused reduce+update and broadcast over
+    cuMem symmetric buffers bound to an NVSwitch multicast object."""
+    world = _world()
+    dtdl.spawn(collectives, nprocs=world, args=(world, str(tmp_path), True))
+    _done_or_skipped(tmp_path, world)
+
+
+def test_nvls_ddp_training(tmp_path):
+    world = _world()
+    dtdl.spawn(ddp_training, nprocs=world, args=(world, str(tmp_path), True, True))
+    _done_or_skipped(tmp_path, world)
+
+
 @pytest.mark.parametrize("use_graph", [False, True])
 def test_ddp_training(tmp_path, use_graph):
     world = _world()

@@ -6,7 +6,7 @@ import pytest
 import distributed_training_dl_b200 as dtdl
 from distributed_training_dl_b200.utils import free_port
 
-from _workers import ddp_equivalence, ddp_pyramidnet
+from _workers import ddp_equivalence, ddp_pyramidnet, fd_channel
 
 
 @pytest.mark.parametrize("init_kind", ["tcp", "env"])
@@ -20,4 +20,11 @@ def test_ddp_equivalence_gloo(tmp_path, init_kind):
 def test_ddp_pyramidnet_gloo(tmp_path):
     world = 2
     dtdl.spawn(ddp_pyramidnet, nprocs=world, args=(world, free_port(), str(tmp_path)), set_env=False)
+    assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_fd_channel(tmp_path, world):
+    """The descriptor all-gather that carries cuMem / multicast handles between ranks."""
+    dtdl.spawn(fd_channel, nprocs=world, args=(world, free_port(), str(tmp_path)), set_env=False)
     assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
