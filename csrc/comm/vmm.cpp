@@ -86,9 +86,14 @@ static CUmulticastObjectProp mc_prop(int world, size_t bytes, int shareable) {
   return p;
 }
 
+// Makes sure `dev` has a primary context, without changing the caller's current device.
 static int ensure_context(int dev) {
-  DTDL_CHECK_CUDA(cudaSetDevice(dev));
-  DTDL_CHECK_CUDA(cudaFree(nullptr));  // forces the primary context into existence
+  int cur = 0;
+  DTDL_CHECK_CUDA(cudaGetDevice(&cur));
+  if (cur != dev) DTDL_CHECK_CUDA(cudaSetDevice(dev));
+  cudaError_t e = cudaFree(nullptr);  // forces the primary context into existence
+  if (cur != dev) cudaSetDevice(cur);
+  DTDL_CHECK_CUDA(e);
   return 0;
 }
 

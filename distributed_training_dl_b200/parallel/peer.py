@@ -44,6 +44,10 @@ class _RawCudaMemory:
 def tensor_from_ptr(ptr: int, nbytes: int, device: torch.device, owner=None) -> torch.Tensor:
     raw = _RawCudaMemory(ptr, nbytes, owner)
     t = torch.as_tensor(raw, device=device)
+    if t.data_ptr() != ptr or t.device != torch.device(device):
+        # torch resolved the pointer to another device and made a copy: the tensor would not
+        # alias the symmetric memory any more
+        raise RuntimeError(f"device pointer {ptr:#x} does not resolve to {device} (torch saw {t.device})")
     t._dtdl_raw = raw  # keep the holder (and thereby the allocation owner) alive
     return t
 
@@ -150,8 +154,10 @@ class PeerComm:
         self._buffers = []
         self.max_blocks = 32        # SM budget of a collective kernel (leaves SMs to backward)
         self.two_shot_min_bytes = 256 * 1024
-        # NVLS: allocate through cuMem + multicast and reduce inside NVSwitch
-        self.use_nvls = world > 1 and os.environ.get("DTDL_NVLS", "0") == "1"
+        # NVLS: allocate through cuMem + multicast and reduce inside NVSwitch.  DTDL_NVLS = 1 / 0
+        # forces it on / off; "auto" (default) turns it on from NVLS_AUTO_MIN_WORLD ranks up when
+        # every rank can join a multicast team (decided in create_multiprocess / create_local).
+        self.use_nvls = False
         self.nvls_min_bytes = int(os.environ.get("DTDL_NVLS_MIN_BYTES", "0"))
         self._fdchan = None
 
@@ -167,6 +173,9 @@ class PeerComm:
             for r, p in enumerate(flags):
                 if r != pc.rank:
                     nv.call("comm_set_peer_flags", pc.handle, r, p)
+            oks = [None] * comm.size
+            dist.all_gather_object(oks, pc._nvls_probe(), group=comm.control)
+            pc._decide_nvls(all(oks))
         return pc
 
     @classmethod
@@ -183,7 +192,39 @@ class PeerComm:
             for r, o in enumerate(comms):
                 if r != c.rank:
                     nv.call("comm_set_peer_flags", c.handle, r, o.flags_ptr)
+        ok = world > 1 and all(c._nvls_probe() for c in comms)
+        for c in comms:
+            c._decide_nvls(ok)
         return comms
+
+    # With 2 ranks the multicast schedule moves 1.5x the bytes of two-shot over NVLink (a rank's own
+    # copy also travels to the switch and back); from 4 ranks up it moves fewer (1 + 1/W vs
+    # 2 (W-1)/W per direction) -- measured in profiles/allreduce_sweep_nvls_{2,8}gpu.md.
+    NVLS_AUTO_MIN_WORLD = 4
+
+    def _nvls_probe(self) -> bool:
+        """Can this rank take part in multicast collectives?  Rank 0 also creates (and drops) a
+        small multicast object: that is the call that fails when the fabric is not set up."""
+        if os.environ.get("DTDL_NVLS", "auto") == "0" or self.world < 2 or not self.multicast_supported():
+            return False
+        dev = self.device.index or 0
+        gran = nv.lib().dtdl_vmm_granularity(dev, self.world)
+        if gran <= 0:
+            return False
+        if self.rank == 0:
+            mc = ctypes.c_longlong()
+            shareable = 0 if self._local_group is not None else 1
+            if nv.lib().dtdl_mc_create(self.world, gran, shareable, ctypes.byref(mc)) != 0:
+                return False
+            nv.lib().dtdl_vmm_release(mc)
+        return True
+
+    def _decide_nvls(self, all_ok: bool):
+        mode = os.environ.get("DTDL_NVLS", "auto")
+        if mode == "1" and not all_ok and self.world > 1:
+            raise nv.NativeError("DTDL_NVLS=1 but a rank cannot join an NVLS multicast team "
+                                 "(no NVSwitch multicast support, or the fabric manager is not running)")
+        self.use_nvls = bool(all_ok and (mode == "1" or (mode == "auto" and self.world >= self.NVLS_AUTO_MIN_WORLD)))
 
     # ------------------------------------------------------------------ IPC plumbing
     def _exchange_ipc(self, local_ptr: int, tag: str):
@@ -295,7 +336,6 @@ class PeerComm:
         world = len(comms)
         size, gran = comms[0]._vmm_size(nbytes)
         idx = [c.device.index or 0 for c in comms]
-        all_devs = (ci * world)(*idx)
         mems = []
         for d in idx:
             h = ll()
@@ -305,20 +345,25 @@ class PeerComm:
         nv.call("mc_create", world, size, 0, ctypes.byref(mc))
         for d in idx:
             nv.call("mc_add_device", mc, d)
-        ptrs = []
         for h in mems:
             nv.call("mc_bind", mc, h, size)
-            out = ctypes.c_void_p()
-            nv.call("vmm_map", h, size, gran, all_devs, world, ctypes.byref(out))
-            ptrs.append(int(out.value))
         bufs = []
         for c, d in zip(comms, idx):
+            # every GPU gets its own virtual ranges (W peer views + the multicast view), each
+            # accessible from that GPU only, so a pointer always resolves to the GPU that uses it
+            dev1 = (ci * 1)(d)
+            ptrs = []
+            for h in mems:
+                out = ctypes.c_void_p()
+                nv.call("vmm_map", h, size, gran, dev1, 1, ctypes.byref(out))
+                ptrs.append(int(out.value))
             out = ctypes.c_void_p()
-            nv.call("vmm_map", mc, size, gran, (ci * 1)(d), 1, ctypes.byref(out))
-            # rank 0's buffer owns the shared mappings and handles
-            own = (size, [int(out.value)] + (ptrs if c.rank == 0 else []), (mems + [mc]) if c.rank == 0 else [])
+            nv.call("vmm_map", mc, size, gran, dev1, 1, ctypes.byref(out))
+            # rank 0's buffer owns the handles
+            own = (size, ptrs + [int(out.value)], (mems + [mc]) if c.rank == 0 else [])
             b = SymmBuffer(c, nbytes, ptrs[c.rank], ptrs, [], mc_ptr=int(out.value), vmm=own)
-            b.bytes.zero_()
+            with torch.cuda.device(c.device):
+                b.bytes.zero_()
             c._buffers.append(b)
             bufs.append(b)
         for c in comms:

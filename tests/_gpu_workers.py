@@ -15,26 +15,29 @@ def _ok(outdir, i):
     open(os.path.join(outdir, f"ok_{i}"), "w").write("ok")
 
 
-def _nvls_or_skip(comm, outdir, i):
-    """NVLS runs need multicast support (NVSwitch + fabric manager); otherwise record a skip."""
-    if comm.peer.multicast_supported():
-        assert comm.peer.use_nvls
-        return True
-    open(os.path.join(outdir, f"skip_{i}"), "w").write("no multicast support")
-    return False
+def _init_nvls(dtdl, outdir, i):
+    """init() with the multicast collectives forced on; None (and a skip marker) where the box has
+    no NVSwitch multicast support -- the forced mode refuses to start there."""
+    os.environ["DTDL_NVLS"] = "1"
+    try:
+        comm = dtdl.init(backend="b200")
+    except Exception as e:  # noqa: BLE001 - only the "not available" refusal is a skip
+        if "cannot join an NVLS multicast team" not in str(e):
+            raise
+        open(os.path.join(outdir, f"skip_{i}"), "w").write(str(e))
+        return None
+    assert comm.peer.use_nvls
+    return comm
 
 
 def collectives(i, world, outdir, nvls=False):
-    if nvls:
-        os.environ["DTDL_NVLS"] = "1"
     import distributed_training_dl_b200 as dtdl
-    comm = dtdl.init(backend="b200")
+    comm = _init_nvls(dtdl, outdir, i) if nvls else dtdl.init(backend="b200")
+    if comm is None:
+        return
     peer = comm.peer
     dev = comm.device
     assert comm.rank == i and peer.world == world
-    if nvls and not _nvls_or_skip(comm, outdir, i):
-        dtdl.shutdown()
-        return
     n = 1 << 20
     buf = peer.alloc(n * 4)
     out = peer.alloc(n * 4)
@@ -113,16 +116,13 @@ def collectives(i, world, outdir, nvls=False):
 
 
 def ddp_training(i, world, outdir, use_graph, nvls=False):
-    if nvls:
-        os.environ["DTDL_NVLS"] = "1"
     import distributed_training_dl_b200 as dtdl
     from distributed_training_dl_b200.engine import CrossEntropyLoss, TrainStep
     from distributed_training_dl_b200.models import MLP, PyramidNet
-    comm = dtdl.init(backend="b200")
-    dev = comm.device
-    if nvls and not _nvls_or_skip(comm, outdir, i):
-        dtdl.shutdown()
+    comm = _init_nvls(dtdl, outdir, i) if nvls else dtdl.init(backend="b200")
+    if comm is None:
         return
+    dev = comm.device
     torch.manual_seed(1 + i)
     # (a) replicas identical after construction although seeded differently
     net = dtdl.wrap(PyramidNet(num_layers=3, alpha=45.0).to(dev))

@@ -51,13 +51,19 @@ def test_ddp_training(tmp_path, use_graph):
     assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
 
 
-def test_data_parallel_engine(tmp_path):
+@pytest.mark.parametrize("nvls", ["0", "1"])
+def test_data_parallel_engine(tmp_path, nvls):
+    """nvls=1: the single-process flavour of the cuMem + multicast allocator (handles shared
+    directly, no descriptor exchange)."""
     _world()
     import subprocess
     import sys
     here = os.path.dirname(os.path.abspath(__file__))
     code = f"import sys; sys.path.insert(0, {here!r}); import _gpu_workers as w; w.data_parallel_engine({str(tmp_path)!r})"
-    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600)
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
+                         env=dict(os.environ, DTDL_NVLS=nvls))
+    if nvls == "1" and "cannot join an NVLS multicast team" in res.stderr:
+        pytest.skip("this box has no NVLS multicast support")
     assert res.returncode == 0 and os.path.exists(tmp_path / "ok_dp"), res.stdout[-2000:] + res.stderr[-4000:]
 
 
