@@ -166,13 +166,13 @@ struct BnApplyArgs {
   int relu, training;
   float* zero_buf;  // scratch of another pass that this launch resets (may be null)
   int zero_n;
+  float* out_sums;  // optional [2*Cp]: sum / sum of squares of y, for the BatchNorm that reads y next
 };
 
-__global__ void bn_apply_kernel(const BnApplyArgs a) {
-  extern __shared__ float ss[];  // scale[Cp], shift[Cp]
+// Per-channel scale/shift into shared memory; block 0 also writes the saved / running statistics
+// and resets `zero_buf`.  Ends with __syncthreads().
+__device__ __forceinline__ void bn_apply_prologue(const BnApplyArgs& a, float* sc, float* sh) {
   const int Cp = a.G * 8;
-  float* sc = ss;
-  float* sh = ss + Cp;
   for (int c = threadIdx.x; c < Cp; c += blockDim.x) {
     float scale = 0.f, shift = 0.f;
     if (c < a.C) {
@@ -205,6 +205,14 @@ __global__ void bn_apply_kernel(const BnApplyArgs a) {
   if (blockIdx.x == 0 && a.zero_buf != nullptr)
     for (int i = threadIdx.x; i < a.zero_n; i += blockDim.x) a.zero_buf[i] = 0.f;
   __syncthreads();
+}
+
+__global__ void bn_apply_kernel(const BnApplyArgs a) {
+  extern __shared__ float ss[];  // scale[Cp], shift[Cp]
+  const int Cp = a.G * 8;
+  float* sc = ss;
+  float* sh = ss + Cp;
+  bn_apply_prologue(a, sc, sh);
 
   const long long total = a.P * a.G;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
@@ -224,6 +232,68 @@ __global__ void bn_apply_kernel(const BnApplyArgs a) {
       for (int k = 0; k < 8; ++k) f.v[k] = fmaxf(f.v[k], 0.f);
     }
     a.y[i] = pack8(f);
+  }
+}
+
+// Same, with the thread layout of bn_stats_kernel (a thread keeps its 8-channel group), so the
+// sums of the values it stores can ride along: the next BatchNorm needs no statistics pass.
+__global__ void bn_apply_stats_kernel(const BnApplyArgs a) {
+  extern __shared__ float ss[];  // scale[Cp], shift[Cp], red[blockDim][16]
+  const int Cp = a.G * 8;
+  float* sc = ss;
+  float* sh = ss + Cp;
+  float* red = ss + 2 * Cp;
+  bn_apply_prologue(a, sc, sh);
+
+  const int G = a.G;
+  const int rows = blockDim.x / G;
+  const int g = threadIdx.x % G, rrow = threadIdx.x / G;
+  float s1[8], s2[8], kscale[8], kshift[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    s1[k] = s2[k] = 0.f;
+    kscale[k] = sc[g * 8 + k];
+    kshift[k] = sh[g * 8 + k];
+  }
+  if (rrow < rows) {
+    for (long long p = (long long)blockIdx.x * rows + rrow; p < a.P; p += (long long)gridDim.x * rows) {
+      F8 f = unpack8(a.x[p * G + g]);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f.v[k] = f.v[k] * kscale[k] + kshift[k];
+      if (a.residual != nullptr && g < a.Gres) {
+        const F8 r = unpack8(a.residual[p * a.Gres + g]);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f.v[k] += r.v[k];
+      }
+      if (a.relu) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) f.v[k] = fmaxf(f.v[k], 0.f);
+      }
+      const uint4 packed = pack8(f);
+      a.y[p * G + g] = packed;
+      const F8 q = unpack8(packed);  // statistics of what the consumer will read (bf16-rounded)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        s1[k] += q.v[k];
+        s2[k] += q.v[k] * q.v[k];
+      }
+    }
+  }
+  float* mine = red + (size_t)threadIdx.x * 16;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    mine[k] = s1[k];
+    mine[8 + k] = s2[k];
+  }
+  __syncthreads();
+  for (int o = threadIdx.x; o < G * 16; o += blockDim.x) {
+    const int og = o / 16, ok = o % 16;
+    float acc = 0.f;
+    for (int rr = 0; rr < rows; ++rr) acc += red[((size_t)rr * G + og) * 16 + ok];
+    if (ok < 8)
+      atomicAdd(&a.out_sums[og * 8 + ok], acc);
+    else
+      atomicAdd(&a.out_sums[Cp + og * 8 + (ok - 8)], acc);
   }
 }
 
@@ -734,6 +804,17 @@ extern "C" int dtdl_bn_apply(const void* x, void* y, const float* sums, const fl
                              const void* residual, int Cres_p, long long P, int C, int Cp, float eps,
                              float momentum, int relu, int training, float* zero_buf, int zero_n,
                              void* stream) {
+  return dtdl_bn_apply_stats(x, y, sums, gamma, beta, running_mean, running_var, num_batches_tracked,
+                             save_mean, save_rstd, residual, Cres_p, P, C, Cp, eps, momentum, relu,
+                             training, zero_buf, zero_n, nullptr, stream);
+}
+
+extern "C" int dtdl_bn_apply_stats(const void* x, void* y, const float* sums, const float* gamma,
+                                   const float* beta, float* running_mean, float* running_var,
+                                   long long* num_batches_tracked, float* save_mean, float* save_rstd,
+                                   const void* residual, int Cres_p, long long P, int C, int Cp,
+                                   float eps, float momentum, int relu, int training, float* zero_buf,
+                                   int zero_n, float* out_sums, void* stream) {
   DTDL_REQUIRE(Cp % 8 == 0 && Cres_p % 8 == 0 && Cres_p <= Cp, "bad channel padding");
   BnApplyArgs a;
   a.x = reinterpret_cast<const uint4*>(x);
@@ -757,6 +838,24 @@ extern "C" int dtdl_bn_apply(const void* x, void* y, const float* sums, const fl
   a.training = training;
   a.zero_buf = zero_buf;
   a.zero_n = zero_n;
+  a.out_sums = out_sums;
+  if (out_sums != nullptr) {
+    DTDL_REQUIRE(Cp <= 8192, "bad channel padding");
+    const int block = block_for_groups(a.G);
+    const int rows = block / a.G;
+    const size_t smem = (size_t)(2 * Cp + block * 16) * sizeof(float);
+    static bool attr[64] = {false};
+    int dev = 0;
+    DTDL_CHECK_CUDA(cudaGetDevice(&dev));
+    if (!attr[dev & 63]) {
+      DTDL_CHECK_CUDA(cudaFuncSetAttribute(bn_apply_stats_kernel,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, 131072));
+      attr[dev & 63] = true;
+    }
+    bn_apply_stats_kernel<<<grid_for(P, rows * 4, kMaxBlocks), block, smem, STREAM(stream)>>>(a);
+    DTDL_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   const long long total = P * a.G;
   bn_apply_kernel<<<grid_for(total, 256 * 4, kMaxBlocks), 256, 2 * Cp * sizeof(float),
                     STREAM(stream)>>>(a);

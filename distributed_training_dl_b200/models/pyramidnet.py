@@ -41,13 +41,16 @@ class PyramidBlock(nn.Module):
         self.bn3 = L.BatchNorm2d(cout)
         # average-pool the shortcut on down-sampling blocks (pytorch/model.py:10-11,19-20)
         self.pool = L.AvgPool2d(2, stride=2, ceil_mode=True) if stride == 2 else None
+        self.next_bn = []   # [BatchNorm2d that consumes this block's output]; a list so that it is
+        #                     not registered as a sub-module (it belongs to the next block)
 
     def forward(self, x):
         shortcut = x if self.pool is None else self.pool(x)
         out = self.conv1(self.bn1(x), stats_for=self.bn2)
         out = self.conv2(self.bn2(out, relu=True), stats_for=self.bn3)
-        # bn3 + shortcut on the first cin channels == out += F.pad(shortcut)
-        return self.bn3(out, residual=shortcut)
+        # bn3 + shortcut on the first cin channels == out += F.pad(shortcut); the BatchNorm that
+        # reads the block's output next (set by PyramidNet) gets its statistics from this pass
+        return self.bn3(out, residual=shortcut, stats_for=self.next_bn[0] if self.next_bn else None)
 
 
 class PyramidNet(nn.Module):
@@ -70,6 +73,10 @@ class PyramidNet(nn.Module):
         self.layer1, self.layer2, self.layer3 = stages
         self.out_channels = cin
         self.bn_out = L.BatchNorm2d(cin)
+        chain = [b for stage in stages for b in stage]
+        for blk, nxt in zip(chain, chain[1:]):
+            blk.next_bn = [nxt.bn1]
+        chain[-1].next_bn = [self.bn_out]
         self.avgpool = L.AvgPool2d(8, stride=1)
         self.fc_out = L.Linear(cin, num_classes)
         self.output = L.OutputLayout(num_classes)
@@ -81,7 +88,7 @@ class PyramidNet(nn.Module):
                 nn.init.constant_(m.bias, 0)
 
     def forward(self, x):
-        x = self.bn1(self.conv1(self.input(x), stats_for=self.bn1))
+        x = self.bn1(self.conv1(self.input(x), stats_for=self.bn1), stats_for=self.layer1[0].bn1)
         x = self.layer3(self.layer2(self.layer1(x)))
         x = self.avgpool(self.bn_out(x, relu=True))
         if not x.is_cuda:

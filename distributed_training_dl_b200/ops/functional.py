@@ -296,7 +296,7 @@ def to_s2d(x: torch.Tensor) -> torch.Tensor:
 # --------------------------------------------------------------------------------------
 class _BatchNorm(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, mod, relu):
+    def forward(ctx, x, gamma, beta, residual, mod, relu, stats_for=None):
         x = x.contiguous()
         N, H, W, Cp = x.shape
         P = N * H * W
@@ -318,12 +318,16 @@ class _BatchNorm(torch.autograd.Function):
         save = torch.empty((2, Cp), dtype=torch.float32, device=x.device)
         mom = mod.momentum if mod.momentum is not None else 0.1
         track = mod.track_running_stats and mod.running_mean is not None
-        nv.call("bn_apply", nv.ptr(x), nv.ptr(y), nv.ptr(stat), nv.ptr(gamma), nv.ptr(beta),
+        out_sums = 0
+        if (stats_for is not None and FUSE_BN_STATS and stats_for is not mod
+                and (stats_for.training or stats_for.running_mean is None)):
+            out_sums = _claim_bn_stats(stats_for, x.device, Cp)
+        nv.call("bn_apply_stats", nv.ptr(x), nv.ptr(y), nv.ptr(stat), nv.ptr(gamma), nv.ptr(beta),
                 nv.ptr(mod.running_mean) if track else 0, nv.ptr(mod.running_var) if track else 0,
                 nv.ptr(mod.num_batches_tracked) if (track and training) else 0,
                 nv.ptr(save[0]), nv.ptr(save[1]), nv.ptr(residual), Cres_p, P, C, Cp, mod.eps, mom,
                 1 if relu else 0, 1 if training else 0,
-                stat[2 * Cp:].data_ptr() if training else 0, 2 * Cp, st)
+                stat[2 * Cp:].data_ptr() if training else 0, 2 * Cp, out_sums, st)
         ctx.mod, ctx.relu, ctx.Cres_p, ctx.training = mod, relu, Cres_p, training
         ctx.save_for_backward(x, y if relu else None, gamma, beta, save)
         return y
@@ -352,11 +356,13 @@ class _BatchNorm(torch.autograd.Function):
         mod._fwd_dirty = False
         _grad_ready(gamma)
         _grad_ready(beta)
-        return dx, None, None, dres, None, None
+        return dx, None, None, dres, None, None, None
 
 
-def batch_norm(x, mod, residual=None, relu=False):
-    return _BatchNorm.apply(x, mod.weight, mod.bias, residual, mod, relu)
+def batch_norm(x, mod, residual=None, relu=False, stats_for=None):
+    """``stats_for``: the training-mode BatchNorm2d that reads this layer's output next; its batch
+    statistics are then accumulated while the output is written."""
+    return _BatchNorm.apply(x, mod.weight, mod.bias, residual, mod, relu, stats_for)
 
 
 # --------------------------------------------------------------------------------------

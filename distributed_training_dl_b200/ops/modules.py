@@ -154,7 +154,7 @@ class BatchNorm2d(nn.BatchNorm2d):
             self._fwd_dirty = False
         return self._stat
 
-    def forward(self, x, residual=None, relu=False):
+    def forward(self, x, residual=None, relu=False, stats_for=None):
         if not is_native(x):
             y = super().forward(x)
             if residual is not None:
@@ -164,7 +164,7 @@ class BatchNorm2d(nn.BatchNorm2d):
                 else:
                     y = torch.cat([y[:, :c] + residual, y[:, c:]], dim=1)
             return F.relu(y) if relu else y
-        return fn.batch_norm(x, self, residual=residual, relu=relu)
+        return fn.batch_norm(x, self, residual=residual, relu=relu, stats_for=stats_for)
 
 
 class AvgPool2d(nn.AvgPool2d):

@@ -86,6 +86,13 @@ int dtdl_bn_apply(const void* x, void* y, const float* sums, const float* gamma,
                   float* save_mean, float* save_rstd, const void* residual, int Cres_p, long long P,
                   int C, int Cp, float eps, float momentum, int relu, int training, float* zero_buf,
                   int zero_n, void* stream);
+/* Same; additionally accumulates sum / sum of squares of the stored y into out_sums[2*Cp]
+ * (pre-zeroed): the statistics of the BatchNorm that opens the next block (pytorch/model.py:27). */
+int dtdl_bn_apply_stats(const void* x, void* y, const float* sums, const float* gamma, const float* beta,
+                  float* running_mean, float* running_var, long long* num_batches_tracked,
+                  float* save_mean, float* save_rstd, const void* residual, int Cres_p, long long P,
+                  int C, int Cp, float eps, float momentum, int relu, int training, float* zero_buf,
+                  int zero_n, float* out_sums, void* stream);
 int dtdl_bn_bwd(const void* dy, const void* x, const void* y, const float* save_mean,
                 const float* save_rstd, const float* gamma, float* sums2 /* [2*Cp], zeroed */,
                 void* dx, void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
