@@ -158,9 +158,16 @@ class Reducer:
         off_b, n = bucket.offset * 4, bucket.numel
         a = self.arena
         if self.peer is not None and self.world > 1:
-            ev = torch.cuda.Event()
-            ev.record(torch.cuda.current_stream(self.device))
-            self.comm_stream.wait_event(ev)
+            # the bucket's gradients may come from three places: the stream this hook runs on, the
+            # user's stream, and the side stream that carries weight gradients during graph capture
+            streams = [torch.cuda.current_stream(self.device)]
+            for extra in (getattr(self, "_user_stream", None), fn.forked_side_stream(self.device)):
+                if extra is not None and all(extra != s for s in streams):
+                    streams.append(extra)
+            for s in streams:
+                ev = torch.cuda.Event()
+                ev.record(s)
+                self.comm_stream.wait_event(ev)
             if self._fused():
                 opt = self.optimizer
                 m = opt._state_flat[opt.state_names[0]]

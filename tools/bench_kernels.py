@@ -62,6 +62,31 @@ def main():
         x_like = torch.randn_like(dy)
         t_bf = timeit(bn_fwd)
         t_bb = timeit(bn_bwd)
+        if os.environ.get("OVERLAP"):
+            # does the weight-gradient kernel overlap with the data-gradient + BN-backward chain when
+            # they sit on two branches of the graph?  (serial = one stream, fork = side stream)
+            side = torch.cuda.Stream()
+
+            def wgrad_on(stream_ptr):
+                nv.call("conv_wgrad", nv.ptr(x), nv.ptr(dy), nv.ptr(gw), nv.ptr(ws), ws.numel(), N, hw, hw, cin,
+                        conv.Cin_p, hw, hw, cout, conv.Cout_p, 3, 3, 1, 1, 0, stream_ptr)
+
+            def serial():
+                wgrad_on(nv.stream_ptr())
+                fn.conv_fprop_raw(dy, conv.wd, conv.Cin_p, 3, 3, 1)
+                bn_bwd()
+
+            def forked():
+                cur = torch.cuda.current_stream()
+                side.wait_stream(cur)
+                wgrad_on(side.cuda_stream)
+                fn.conv_fprop_raw(dy, conv.wd, conv.Cin_p, 3, 3, 1)
+                bn_bwd()
+                cur.wait_stream(side)
+
+            t_s, t_k = timeit(serial), timeit(forked)
+            print(f"{str((cin, cout, hw)):>22s} wgrad+dgrad+bn_bwd: one stream {t_s:7.1f} us, forked {t_k:7.1f} us "
+                  f"({100 * (1 - t_k / t_s):.0f} % less)")
         nbytes = N * hw * hw * conv.Cout_p * 2
         print(f"{str((cin, cout, hw)):>22s} {t_f:9.1f} {flops / t_f / 1e6:6.0f} {t_d:9.1f} {t_w:9.1f} {flops / t_w / 1e6:6.0f} "
               f"{t_bf:7.1f} {t_bb:7.1f} {nbytes * 9 / (t_bf + t_bb) / 1e3:6.0f}")
