@@ -25,41 +25,128 @@ struct PackEntry {
 
 static constexpr int kPackBlock = 256;
 static constexpr int kPackPerBlock = 256 * 8;
+// Tiled path (taps <= kTileMaxTaps): one block stages a 32 (co) x 32 (ci) x taps cube of the fp32
+// weights in shared memory with row-contiguous loads, then writes its piece of both packs in
+// 64-byte runs.  The element-wise path below reads the source with a stride of `taps` floats for
+// the fprop pack and of a whole filter row for the dgrad pack and divides per element (200 us for
+// PyramidNet's 28.5 M weights; the tiled path: 112 us).
+static constexpr int kTile = 32;
+static constexpr int kTileMaxTaps = 9;
 
-__global__ void pack_weights_kernel(const PackEntry* __restrict__ table, int n_entries) {
-  // locate the entry owning this block (tables are small: linear scan from a guess)
-  int lo = 0, hi = n_entries - 1;
-  while (lo < hi) {
-    const int mid = (lo + hi + 1) >> 1;
-    if (table[mid].first_block <= (long long)blockIdx.x)
-      lo = mid;
-    else
-      hi = mid - 1;
+// TAPS > 0: compile-time filter size (index arithmetic becomes multiplies and shifts -- with run-time
+// divisors the kernel is bound by integer division, not by memory); TAPS = 0: any size.
+template <int TAPS>
+__device__ __forceinline__ void pack_tile(const PackEntry& e, long long tile, float* s) {
+  const int taps = TAPS ? TAPS : e.taps;
+  const int tiles_ci = (e.Cin_p16 + kTile - 1) / kTile;
+  const int co0 = (int)(tile / tiles_ci) * kTile, ci0 = (int)(tile % tiles_ci) * kTile;
+  const int row = kTile * taps;   // floats of one co row of the cube
+  const int rstride = row + 1;    // +1: the dgrad pass walks down a column
+  // fixed roles, no per-element index division: a warp owns rows (or columns) w, w+8, ...
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int kvalid = (e.Cin - ci0 < kTile ? (e.Cin - ci0 > 0 ? e.Cin - ci0 : 0) : kTile) * taps;
+  for (int r = w; r < kTile; r += kPackBlock / 32) {
+    const int co = co0 + r;
+    const float* src = e.w + ((long long)co * e.Cin + ci0) * taps;
+#pragma unroll 3
+    for (int k = lane; k < row; k += 32)
+      s[r * rstride + k] = (co < e.Cout && k < kvalid) ? src[k] : 0.f;
   }
-  const PackEntry e = table[lo];
-  const long long base = ((long long)blockIdx.x - e.first_block) * kPackPerBlock;
-  const long long total = e.f_elems + (e.wd ? e.d_elems : 0);
-  for (int k = 0; k < 8; ++k) {
-    const long long i = base + k * kPackBlock + threadIdx.x;
-    if (i >= total) return;
-    if (i < e.f_elems) {
-      const int ci = (int)(i % e.Cin_p);
-      const long long r = i / e.Cin_p;
-      const int t = (int)(r % e.taps);
-      const int co = (int)(r / e.taps);
-      float v = 0.f;
-      if (co < e.Cout && ci < e.Cin) v = e.w[((long long)co * e.Cin + ci) * e.taps + t];
-      e.wf[i] = __float2bfloat16(v);
-    } else {
-      const long long j = i - e.f_elems;
-      const int co = (int)(j % e.Cout_p);
-      const long long r = j / e.Cout_p;
-      const int t = (int)(r % e.taps);
-      const int ci = (int)(r / e.taps);
-      float v = 0.f;
-      if (co < e.Cout && ci < e.Cin)
-        v = e.w[((long long)co * e.Cin + ci) * e.taps + (e.taps - 1 - t)];
-      e.wd[j] = __float2bfloat16(v);
+  __syncthreads();
+  // fprop pack: wf[co][t][ci], lanes run along ci
+  {
+    const int ci = ci0 + lane;
+    if (ci < e.Cin_p) {
+      for (int r = w; r < kTile; r += kPackBlock / 32) {
+        const int co = co0 + r;
+        if (co >= e.Cout_p16) break;
+        __nv_bfloat16* dst = e.wf + (long long)co * taps * e.Cin_p + ci;
+        const float* sp = s + r * rstride + lane * taps;
+#pragma unroll
+        for (int t = 0; t < (TAPS ? TAPS : 1); ++t) dst[(long long)t * e.Cin_p] = __float2bfloat16(sp[t]);
+        if (!TAPS)
+          for (int t = 1; t < taps; ++t) dst[(long long)t * e.Cin_p] = __float2bfloat16(sp[t]);
+      }
+    }
+  }
+  // dgrad pack: wd[ci][t'][co] = w[co][ci][taps-1-t'], lanes run along co
+  if (e.wd != nullptr) {
+    const int co = co0 + lane;
+    if (co < e.Cout_p) {
+      for (int cl = w; cl < kTile; cl += kPackBlock / 32) {
+        const int ci = ci0 + cl;
+        if (ci >= e.Cin_p16) break;
+        __nv_bfloat16* dst = e.wd + (long long)ci * taps * e.Cout_p + co;
+        const float* sp = s + lane * rstride + cl * taps + (taps - 1);
+#pragma unroll
+        for (int t = 0; t < (TAPS ? TAPS : 1); ++t) dst[(long long)t * e.Cout_p] = __float2bfloat16(sp[-t]);
+        if (!TAPS)
+          for (int t = 1; t < taps; ++t) dst[(long long)t * e.Cout_p] = __float2bfloat16(sp[-t]);
+      }
+    }
+  }
+}
+
+static constexpr int kMaxSmemEntries = 1024;
+
+// Persistent blocks walk the global list of work items (tiles, or 2048-element runs for large
+// filters).  Which layer an item belongs to is a binary search over the layers' first-item prefix
+// sums, staged once per block in shared memory: searching the table in global memory cost eight
+// dependent L2 round trips per item and was, at 28 K items, what the whole kernel waited for.
+__global__ void __launch_bounds__(kPackBlock)
+pack_weights_kernel(const PackEntry* __restrict__ table, int n_entries, long long total_blocks) {
+  __shared__ float s_tile[kTile * (kTile * kTileMaxTaps + 1)];
+  __shared__ long long s_first[kMaxSmemEntries];
+  const bool staged = n_entries <= kMaxSmemEntries;
+  if (staged)
+    for (int i = threadIdx.x; i < n_entries; i += kPackBlock) s_first[i] = table[i].first_block;
+  __syncthreads();
+  for (long long item = blockIdx.x; item < total_blocks; item += gridDim.x) {
+    int lo = 0, hi = n_entries - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      const long long fb = staged ? s_first[mid] : table[mid].first_block;
+      if (fb <= item)
+        lo = mid;
+      else
+        hi = mid - 1;
+    }
+    const PackEntry e = table[lo];
+    if (e.taps <= kTileMaxTaps) {
+      const long long tile = item - e.first_block;
+      if (e.taps == 9)
+        pack_tile<9>(e, tile, s_tile);
+      else if (e.taps == 1)
+        pack_tile<1>(e, tile, s_tile);
+      else
+        pack_tile<0>(e, tile, s_tile);
+      __syncthreads();  // the next item overwrites the tile
+      continue;
+    }
+    const long long base = (item - e.first_block) * kPackPerBlock;
+    const long long total = e.f_elems + (e.wd ? e.d_elems : 0);
+    for (int k = 0; k < 8; ++k) {
+      const long long i = base + k * kPackBlock + threadIdx.x;
+      if (i >= total) break;
+      if (i < e.f_elems) {
+        const int ci = (int)(i % e.Cin_p);
+        const long long r = i / e.Cin_p;
+        const int t = (int)(r % e.taps);
+        const int co = (int)(r / e.taps);
+        float v = 0.f;
+        if (co < e.Cout && ci < e.Cin) v = e.w[((long long)co * e.Cin + ci) * e.taps + t];
+        e.wf[i] = __float2bfloat16(v);
+      } else {
+        const long long j = i - e.f_elems;
+        const int co = (int)(j % e.Cout_p);
+        const long long r = j / e.Cout_p;
+        const int t = (int)(r % e.taps);
+        const int ci = (int)(r / e.taps);
+        float v = 0.f;
+        if (co < e.Cout && ci < e.Cin)
+          v = e.w[((long long)co * e.Cin + ci) * e.taps + (e.taps - 1 - t)];
+        e.wd[j] = __float2bfloat16(v);
+      }
     }
   }
 }
@@ -88,6 +175,8 @@ extern "C" long long dtdl_pack_entry_fill(void* entry, const float* w, void* wf,
   e->f_elems = (long long)e->Cout_p16 * taps * Cin_p;
   e->d_elems = (long long)e->Cin_p16 * taps * Cout_p;
   e->first_block = first_block;
+  if (taps <= kTileMaxTaps)
+    return (long long)((e->Cout_p16 + kTile - 1) / kTile) * ((e->Cin_p16 + kTile - 1) / kTile);
   const long long total = e->f_elems + (wd ? e->d_elems : 0);
   return (total + kPackPerBlock - 1) / kPackPerBlock;
 }
@@ -95,9 +184,10 @@ extern "C" long long dtdl_pack_entry_fill(void* entry, const float* w, void* wf,
 extern "C" int dtdl_pack_weights(const void* device_table, int n_entries, long long total_blocks,
                                  void* stream) {
   DTDL_REQUIRE(n_entries > 0 && total_blocks > 0 && total_blocks < (1ll << 31), "bad pack table");
-  pack_weights_kernel<<<(unsigned)total_blocks, kPackBlock, 0,
-                        reinterpret_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<const PackEntry*>(device_table), n_entries);
+  const long long resident = (long long)sm_count() * 5;  // 45 KB of shared memory per block
+  const unsigned grid = (unsigned)(total_blocks < resident ? total_blocks : resident);
+  pack_weights_kernel<<<grid, kPackBlock, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const PackEntry*>(device_table), n_entries, total_blocks);
   DTDL_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
