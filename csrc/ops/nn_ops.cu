@@ -372,6 +372,7 @@ struct BnBwdArgs {
   int C, G, relu;
   float* zero_buf;
   int zero_n;
+  const uint4* add_in;  // optional [P][Cp]: another gradient of the same input, summed into dx
 };
 
 __global__ void bn_bwd_apply_kernel(const BnBwdArgs a) {
@@ -426,6 +427,11 @@ __global__ void bn_bwd_apply_kernel(const BnBwdArgs a) {
       const int c = g * 8 + k;
       const float xhat = (xv.v[k] - mm[c]) * rr[c];
       o.v[k] = k1[c] * (d.v[k] - k2[c] - xhat * k3[c]);
+    }
+    if (a.add_in != nullptr) {
+      const F8 e = unpack8(a.add_in[i]);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) o.v[k] += e.v[k];
     }
     a.dx[i] = pack8(o);
   }
@@ -868,6 +874,16 @@ extern "C" int dtdl_bn_bwd(const void* dy, const void* x, const void* y, const f
                            void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
                            long long P, int C, int Cp, int relu, float* zero_buf, int zero_n,
                            void* stream) {
+  return dtdl_bn_bwd_add(dy, x, y, save_mean, save_rstd, gamma, sums2, dx, dres, Cres_p, dgamma, dbeta,
+                         accumulate, P, C, Cp, relu, zero_buf, zero_n, nullptr, stream);
+}
+
+extern "C" int dtdl_bn_bwd_add(const void* dy, const void* x, const void* y, const float* save_mean,
+                           const float* save_rstd, const float* gamma, float* sums2, void* dx,
+                           void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
+                           long long P, int C, int Cp, int relu, float* zero_buf, int zero_n,
+                           const void* add_in,
+                               void* stream) {
   DTDL_REQUIRE(Cp % 8 == 0 && Cres_p % 8 == 0 && Cres_p <= Cp && Cp <= 8192, "bad channel padding");
   DTDL_REQUIRE(!relu || y != nullptr, "relu backward needs the saved output");
   const int G = Cp / 8;
@@ -900,6 +916,7 @@ extern "C" int dtdl_bn_bwd(const void* dy, const void* x, const void* y, const f
   a.relu = relu;
   a.zero_buf = zero_buf;
   a.zero_n = zero_n;
+  a.add_in = reinterpret_cast<const uint4*>(add_in);
   const long long total = P * G;
   bn_bwd_apply_kernel<<<grid_for(total, 256 * 4, kMaxBlocks), 256, 5 * Cp * sizeof(float),
                         STREAM(stream)>>>(a);

@@ -45,8 +45,11 @@ class PyramidBlock(nn.Module):
         #                     not registered as a sub-module (it belongs to the next block)
 
     def forward(self, x):
-        shortcut = x if self.pool is None else self.pool(x)
-        out = self.conv1(self.bn1(x), stats_for=self.bn2)
+        if self.pool is None:
+            h, shortcut = self.bn1(x, fork_input=True)   # shortcut == x; its gradient joins bn1's
+        else:
+            h, shortcut = self.bn1(x), self.pool(x)
+        out = self.conv1(h, stats_for=self.bn2)
         out = self.conv2(self.bn2(out, relu=True), stats_for=self.bn3)
         # bn3 + shortcut on the first cin channels == out += F.pad(shortcut); the BatchNorm that
         # reads the block's output next (set by PyramidNet) gets its statistics from this pass

@@ -354,7 +354,7 @@ def to_s2d(x: torch.Tensor) -> torch.Tensor:
 # --------------------------------------------------------------------------------------
 class _BatchNorm(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, mod, relu, stats_for=None):
+    def forward(ctx, x, gamma, beta, residual, mod, relu, stats_for=None, fork_input=False):
         x = x.contiguous()
         N, H, W, Cp = x.shape
         P = N * H * W
@@ -388,13 +388,20 @@ class _BatchNorm(torch.autograd.Function):
                 stat[2 * Cp:].data_ptr() if training else 0, 2 * Cp, out_sums, st)
         ctx.mod, ctx.relu, ctx.Cres_p, ctx.training = mod, relu, Cres_p, training
         ctx.save_for_backward(x, y if relu else None, gamma, beta, save)
+        if fork_input:
+            # second output = the input itself (the identity shortcut of a residual block): its
+            # gradient comes back to this node and is summed into dx by the backward kernel
+            return y, x.view_as(x)
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dalias=None):
         mod = ctx.mod
         x, y, gamma, beta, save = ctx.saved_tensors
+        if dy is None:      # only the shortcut output was used
+            return dalias, None, None, None, None, None, None, None
         dy = dy.contiguous()
+        add_in = dalias.contiguous() if dalias is not None else None
         N, H, W, Cp = x.shape
         P = N * H * W
         st = nv.stream_ptr()
@@ -407,20 +414,21 @@ class _BatchNorm(torch.autograd.Function):
         dres = None
         if ctx.Cres_p and ctx.needs_input_grad[3]:
             dres = torch.empty((N, H, W, ctx.Cres_p), dtype=torch.bfloat16, device=x.device)
-        nv.call("bn_bwd", nv.ptr(dy), nv.ptr(x), nv.ptr(y), nv.ptr(save[0]), nv.ptr(save[1]),
+        nv.call("bn_bwd_add", nv.ptr(dy), nv.ptr(x), nv.ptr(y), nv.ptr(save[0]), nv.ptr(save[1]),
                 nv.ptr(gamma), stat[2 * Cp:].data_ptr(), nv.ptr(dx), nv.ptr(dres), ctx.Cres_p,
                 nv.ptr(gg), nv.ptr(gb), 1 if (acc_g or acc_b) else 0, P, mod.num_features, Cp,
-                1 if ctx.relu else 0, nv.ptr(stat), 2 * Cp, st)
+                1 if ctx.relu else 0, nv.ptr(stat), 2 * Cp, nv.ptr(add_in), st)
         mod._fwd_dirty = False
         _grad_ready(gamma)
         _grad_ready(beta)
-        return dx, None, None, dres, None, None, None
+        return dx, None, None, dres, None, None, None, None
 
 
-def batch_norm(x, mod, residual=None, relu=False, stats_for=None):
+def batch_norm(x, mod, residual=None, relu=False, stats_for=None, fork_input=False):
     """``stats_for``: the training-mode BatchNorm2d that reads this layer's output next; its batch
-    statistics are then accumulated while the output is written."""
-    return _BatchNorm.apply(x, mod.weight, mod.bias, residual, mod, relu, stats_for)
+    statistics are then accumulated while the output is written.  ``fork_input``: returns
+    ``(y, x)`` where the second item stands for the input on the identity-shortcut path."""
+    return _BatchNorm.apply(x, mod.weight, mod.bias, residual, mod, relu, stats_for, fork_input)
 
 
 # --------------------------------------------------------------------------------------

@@ -154,8 +154,13 @@ class BatchNorm2d(nn.BatchNorm2d):
             self._fwd_dirty = False
         return self._stat
 
-    def forward(self, x, residual=None, relu=False, stats_for=None):
+    def forward(self, x, residual=None, relu=False, stats_for=None, fork_input=False):
+        """``fork_input=True`` returns ``(y, x')``: use ``x'`` as the block's identity shortcut and the
+        shortcut's gradient is added to this layer's input gradient inside the backward kernel
+        instead of by a separate autograd add."""
         if not is_native(x):
+            if fork_input:
+                return self.forward(x, residual=residual, relu=relu), x
             y = super().forward(x)
             if residual is not None:
                 c = residual.shape[1]
@@ -164,7 +169,7 @@ class BatchNorm2d(nn.BatchNorm2d):
                 else:
                     y = torch.cat([y[:, :c] + residual, y[:, c:]], dim=1)
             return F.relu(y) if relu else y
-        return fn.batch_norm(x, self, residual=residual, relu=relu, stats_for=stats_for)
+        return fn.batch_norm(x, self, residual=residual, relu=relu, stats_for=stats_for, fork_input=fork_input)
 
 
 class AvgPool2d(nn.AvgPool2d):

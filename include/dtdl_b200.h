@@ -97,6 +97,12 @@ int dtdl_bn_bwd(const void* dy, const void* x, const void* y, const float* save_
                 const float* save_rstd, const float* gamma, float* sums2 /* [2*Cp], zeroed */,
                 void* dx, void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
                 long long P, int C, int Cp, int relu, float* zero_buf, int zero_n, void* stream);
+/* Same; dx additionally receives add_in (bf16, shape of x): the gradient that reaches the same
+ * tensor through the identity shortcut (pytorch/model.py:37,49), so autograd needs no add pass. */
+int dtdl_bn_bwd_add(const void* dy, const void* x, const void* y, const float* save_mean,
+                const float* save_rstd, const float* gamma, float* sums2 /* [2*Cp], zeroed */,
+                void* dx, void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
+                long long P, int C, int Cp, int relu, float* zero_buf, int zero_n, const void* add_in, void* stream);
 int dtdl_relu_bwd(const void* dy, const void* y, void* dx, long long n_elems, void* stream);
 int dtdl_add_bf16(const void* a, const void* b, void* out, long long n_elems, void* stream);
 int dtdl_add_prefix_bf16(void* a, const void* b, long long P, int Ca_p, int Cb_p, void* stream);

@@ -165,6 +165,12 @@ def test_batchnorm_forward_backward(C, Cres, relu, HW, N):
     assert not nxt_a._stats_from_producer
     assert _rel_err(za.float(), zb.float()) < 1e-2
     assert torch.allclose(nxt_a.running_var, nxt_b.running_var, rtol=1e-3, atol=1e-4)
+    # identity-shortcut fork: the shortcut's gradient is summed into dx by the backward kernel
+    xf = fn.to_nhwc(x).requires_grad_(True)
+    yf, xs = bn(xf, residual=rn.detach() if Cres else None, relu=relu, fork_input=True)
+    dz = _bf(torch.randn_like(x))
+    torch.autograd.backward([yf, xs], [fn.to_nhwc(dy), fn.to_nhwc(dz)])
+    assert _rel_err(_nhwc_to_nchw(xf.grad, C), rx.grad + dz) < 3e-2
     # second step exercises the folded re-zeroing of the statistics scratch
     y2 = bn(xn, residual=rn, relu=relu)
     ry2 = ref(rx)
