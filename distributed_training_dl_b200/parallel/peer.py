@@ -152,7 +152,8 @@ class PeerComm:
         self._local_group = None    # list of sibling PeerComm (single-process mode)
         self._seq = 0
         self._buffers = []
-        self.max_blocks = 32        # SM budget of a collective kernel (leaves SMs to backward)
+        # SM budget of a collective kernel (leaves SMs to backward)
+        self.max_blocks = int(os.environ.get("DTDL_COMM_BLOCKS", "32"))
         self.two_shot_min_bytes = 256 * 1024
         # NVLS: allocate through cuMem + multicast and reduce inside NVSwitch.  DTDL_NVLS = 1 / 0
         # forces it on / off; "auto" (default) turns it on from NVLS_AUTO_MIN_WORLD ranks up when

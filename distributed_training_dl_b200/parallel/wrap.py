@@ -36,6 +36,11 @@ class Reducer:
     all ranks issue the same sequence of collectives whatever the local gradient order."""
 
     def __init__(self, module, comm, bucket_cap_mb=25.0, first_bucket_mb=1.0, broadcast_buffers=True):
+        # tuning overrides for measurements (tools/sweep_2gpu.sh): bucket sizes, buffer broadcast
+        bucket_cap_mb = float(os.environ.get("DTDL_BUCKET_MB", bucket_cap_mb))
+        first_bucket_mb = float(os.environ.get("DTDL_FIRST_BUCKET_MB", first_bucket_mb))
+        if os.environ.get("DTDL_BROADCAST_BUFFERS") == "0":
+            broadcast_buffers = False
         self.module, self.comm = module, comm
         self.world, self.rank = comm.size, comm.rank
         self.device = next(module.parameters()).device

@@ -203,3 +203,15 @@ def test_wrap_with_torch_optimizer_cpu():
         ropt.step()
     for a, b in zip(net.module.parameters(), ref.parameters()):
         assert torch.allclose(a, b, atol=1e-6)
+
+
+def test_native_library_resolves_every_symbol():
+    """dlopen with RTLD_NOW: an unresolved symbol in libdtdl_b200.so must fail here, on the build
+    machine, not on the GPU box; and every prototype of the header must exist in the library."""
+    import ctypes
+    from distributed_training_dl_b200 import _native as nv
+    if not nv.available():
+        pytest.skip("library not built")
+    handle = ctypes.CDLL(nv.LIB_PATH, mode=ctypes.RTLD_GLOBAL | 2)   # 2 = RTLD_NOW
+    for name in nv._parse_header(nv.HEADER_PATH):
+        assert hasattr(handle, name), name
