@@ -143,9 +143,16 @@ def run_ours(args):
                "ms_per_step": ms2 / args.steps,
                "h2d_bytes_per_step": world * (xs[0].numel() * 4 + ts[0].numel() * 8),
                "d2h_bytes_per_step": world * 4, "last_loss": float(host_loss.item())}
+    peer = getattr(comm, "peer", None)
+    if world == 1:
+        comm_kind = "none (fused SGD update kernel)"
+    elif peer is not None and peer.use_nvls:
+        comm_kind = "NVLS multimem.ld_reduce/st fused allreduce+SGD (NVSwitch multicast)"
+    else:
+        comm_kind = "peer-memory two-shot fused allreduce+SGD (NVLink P2P)"
     res = result_line(args, "ours", world, value, ms, clocks, e2e, launches, dtype="bf16",
                       extra={"graph": not args.no_graph, "kernels_per_step": step.launches_per_step,
-                             "parallelism": f"dp{world}", "comm": "peer-memory fused allreduce+SGD (NVLink)"})
+                             "parallelism": f"dp{world}", "comm": comm_kind})
     if rank == 0:
         print(json.dumps(res), flush=True)
     torch.cuda.synchronize()
