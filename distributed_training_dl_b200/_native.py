@@ -15,7 +15,8 @@ import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _ROOT = os.path.dirname(_HERE)
-LIB_PATH = os.path.join(_HERE, "lib", "libdtdl_b200.so")
+# DTDL_LIB: load another build of the library (A/B measurements of kernel variants)
+LIB_PATH = os.environ.get("DTDL_LIB") or os.path.join(_HERE, "lib", "libdtdl_b200.so")
 HEADER_PATH = os.path.join(_ROOT, "include", "dtdl_b200.h")
 
 _lock = threading.Lock()

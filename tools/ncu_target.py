@@ -18,6 +18,10 @@ for _ in range(4):
     y = fn.conv_fprop_raw(x, conv.wf, conv.Cout_p, 3, 3, 1)
     nv.call("conv_wgrad", nv.ptr(x), nv.ptr(dy), nv.ptr(gw), nv.ptr(ws), ws.numel(), N, hw, hw, cin, conv.Cin_p,
             hw, hw, cout, conv.Cout_p, 3, 3, 1, 1, 0, nv.stream_ptr())
+# the same convolution with the BatchNorm statistics epilogue (what training runs), twice
+stat = torch.zeros(2 * conv.Cout_p, device="cuda")
+for _ in range(2):
+    y = fn.conv_fprop_raw(x, conv.wf, conv.Cout_p, 3, 3, 1, stats=stat.data_ptr())
 # bandwidth-bound kernels on the same shape: BN forward (stats + apply) and backward, fused SGD
 from distributed_training_dl_b200.ops import BatchNorm2d
 bn = BatchNorm2d(cout).cuda()
@@ -25,6 +29,17 @@ xb = dy.clone().requires_grad_(True)
 for _ in range(2):
     yb = bn(xb, relu=True)
     yb.backward(dy)
+nxt = BatchNorm2d(cout).cuda()
+with torch.no_grad():
+    for _ in range(2):
+        nxt(bn(xb, relu=True, stats_for=nxt))       # bn_apply_stats_kernel
+# weight pack of a whole PyramidNet (one launch)
+from distributed_training_dl_b200.models import pyramidnet
+from distributed_training_dl_b200.ops.modules import pack_weights, packed_layers
+net = pyramidnet().cuda()
+cache = {}
+for _ in range(2):
+    pack_weights(packed_layers(net), cache)
 p = torch.randn(1 << 24, device="cuda"); g = torch.randn_like(p); m = torch.zeros_like(p)
 hyper = torch.tensor([0.1, 0.9, 1e-4, 1.0] + [0.0] * 12, device="cuda")
 for _ in range(2):
