@@ -146,15 +146,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       umma_commit(tmem_full);
     }
-  }
-  // After the main loop all eight warps drain the accumulator: warps 4-7 convert and store the
-  // tile; warps 0-3 (producer, MMA issuer, allocator and a spare -- idle by now) read the same
-  // TMEM quadrants (a warp may access the 32 lanes of quadrant warp % 4) and reduce the
-  // BatchNorm statistics, so the statistics cost no time on the store warps' critical path.
-  __syncwarp();
-  {
-    const bool stats_warp = warp < 4;
-    const int q = warp & 3;
+  } else if (warp >= 4) {
+    const int q = warp - 4;
     const int row = q * 32 + lane;
     const int wi = row % a.BW;
     const int hi = (row / a.BW) % a.BH;
@@ -166,16 +159,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const bool f32 = a.flags & 2;
 
     __shared__ float s_sums[512];
-    const int etid = threadIdx.x;   // statistics warps are threads 0..127
-    const bool do_stats = stats_warp && a.stats != nullptr;
-    if (do_stats) epilogue_stats_init(s_sums, a.n_tile, etid);
-    const int n_chunks = (stats_warp && !do_stats) ? 0 : a.n_tile / 16;
-    if (n_chunks) {
-      mbar_wait(tmem_full, 0, 3);
-      tc_fence_after();
-    }
+    const int etid = threadIdx.x - 128;
+    if (a.stats != nullptr) epilogue_stats_init(s_sums, a.n_tile, etid);
+    mbar_wait(tmem_full, 0, 3);
+    tc_fence_after();
     const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
-    for (int j = 0; j < n_chunks; ++j) {
+    for (int j = 0; j < a.n_tile / 16; ++j) {
       uint32_t v[16];
       tmem_ld16(lane_base + j * 16, v);
       tmem_ld_wait();
@@ -187,10 +176,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (a.bias != nullptr && col0 + i < a.Cout_p) f[i] += a.bias[col0 + i];
         if (relu) f[i] = fmaxf(f[i], 0.f);
       }
-      if (stats_warp) {
-        epilogue_col_stats(f, valid, lane, s_sums, a.n_tile, j * 16);
-        continue;
-      }
+      if (a.stats != nullptr) epilogue_col_stats(f, valid, lane, s_sums, a.n_tile, j * 16);
       if (!valid) continue;
       if (f32) {
         float* out = reinterpret_cast<float*>(a.y) + pix * a.Cout_p + col0;
@@ -216,7 +202,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
     }
-    if (do_stats) epilogue_stats_flush(s_sums, a.stats, a.n_tile, nt * a.n_tile, a.Cout_p, etid);
+    if (a.stats != nullptr) epilogue_stats_flush(s_sums, a.stats, a.n_tile, nt * a.n_tile, a.Cout_p, etid);
   }
 
   tc_fence_before();

@@ -134,30 +134,20 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       umma_commit(tmem_full);
     }
-  }
-  // All eight warps drain the accumulators: warps 4-7 convert and store, warps 0-3 (idle after the
-  // main loop) read the same TMEM quadrants (quadrant = warp % 4) and reduce the BatchNorm
-  // statistics off the store warps' critical path.
-  __syncwarp();
-  {
-    const bool stats_warp = warp < 4;
-    const int q = warp & 3;
+  } else if (warp >= 4) {
+    const int q = warp - 4;
     const int row = q * 32 + lane;
     const int wo = row % a.BW;
     const int hi = row / a.BW;
     const bool relu = a.flags & 1;
     const bool f32 = a.flags & 2;
     __shared__ float s_sums[512];
-    const int etid = threadIdx.x;   // statistics warps are threads 0..127
-    const bool do_stats = stats_warp && a.stats != nullptr;
-    if (do_stats) epilogue_stats_init(s_sums, a.n_tile, etid);
-    const int n_sub = (stats_warp && !do_stats) ? 0 : a.MS;
-    if (n_sub) {
-      mbar_wait(tmem_full, 0, 23);
-      tc_fence_after();
-    }
+    const int etid = threadIdx.x - 128;
+    if (a.stats != nullptr) epilogue_stats_init(s_sums, a.n_tile, etid);
+    mbar_wait(tmem_full, 0, 23);
+    tc_fence_after();
     const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
-    for (int m = 0; m < n_sub; ++m) {
+    for (int m = 0; m < a.MS; ++m) {
       const int ho = h0 + m * a.BH + hi;
       const bool valid = ho < a.Ho && wo < a.Wo;
       const size_t pix = ((size_t)n_img * a.Ho + ho) * a.Wo + wo;
@@ -173,10 +163,7 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (a.bias != nullptr && col0 + i < a.Cout_p) f[i] += a.bias[col0 + i];
           if (relu) f[i] = fmaxf(f[i], 0.f);
         }
-        if (stats_warp) {
-          epilogue_col_stats(f, valid, lane, s_sums, a.n_tile, j * 16);
-          continue;
-        }
+        if (a.stats != nullptr) epilogue_col_stats(f, valid, lane, s_sums, a.n_tile, j * 16);
         if (!valid) continue;
         if (f32) {
           float* out = reinterpret_cast<float*>(a.y) + pix * a.Cout_p + col0;
@@ -203,7 +190,7 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
     }
-    if (do_stats) epilogue_stats_flush(s_sums, a.stats, a.n_tile, nt * a.n_tile, a.Cout_p, etid);
+    if (a.stats != nullptr) epilogue_stats_flush(s_sums, a.stats, a.n_tile, nt * a.n_tile, a.Cout_p, etid);
   }
 
   tc_fence_before();
