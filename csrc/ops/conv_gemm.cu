@@ -158,9 +158,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const bool relu = a.flags & 1;
     const bool f32 = a.flags & 2;
 
-    __shared__ float s_sums[512];
+    // statistics scratch = the pipeline's stage memory (free once the accumulator is complete)
+    float* s_parts = reinterpret_cast<float*>(sA);
     const int etid = threadIdx.x - 128;
-    if (a.stats != nullptr) epilogue_stats_init(s_sums, a.n_tile, etid);
     mbar_wait(tmem_full, 0, 3);
     tc_fence_after();
     const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
@@ -176,7 +176,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (a.bias != nullptr && col0 + i < a.Cout_p) f[i] += a.bias[col0 + i];
         if (relu) f[i] = fmaxf(f[i], 0.f);
       }
-      if (a.stats != nullptr) epilogue_col_stats(f, valid, lane, s_sums, a.n_tile, j * 16);
+      if (a.stats != nullptr)
+        epilogue_col_stats_part(f, valid, lane, s_parts + q * 2 * a.n_tile, a.n_tile, j * 16, true);
       if (!valid) continue;
       if (f32) {
         float* out = reinterpret_cast<float*>(a.y) + pix * a.Cout_p + col0;
@@ -202,7 +203,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
     }
-    if (a.stats != nullptr) epilogue_stats_flush(s_sums, a.stats, a.n_tile, nt * a.n_tile, a.Cout_p, etid);
+    if (a.stats != nullptr) epilogue_stats_flush_parts(s_parts, a.stats, a.n_tile, nt * a.n_tile, a.Cout_p, etid);
   }
 
   tc_fence_before();

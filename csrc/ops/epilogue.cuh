@@ -36,6 +36,25 @@ __device__ __forceinline__ void epilogue_col_stats(const float (&f)[16], bool va
   atomicAdd(&s_sums[(lane < 16 ? 0 : n_tile) + jcol + (lane & 15)], tot);
 }
 
+// Atomic-free accumulation inside the CTA: every epilogue warp owns one row part[2*n_tile] of a
+// scratch area (the kernels lend their pipeline stage memory, idle once the accumulator is
+// complete); lane L writes the warp total of column/quantity L with a plain store.  Shared-memory
+// float atomics are compare-and-swap loops, and four warps hitting the same 32 words every chunk
+// made them the dominant cost of the statistics epilogue.
+__device__ __forceinline__ void epilogue_col_stats_part(const float (&f)[16], bool valid, int lane,
+                                                        float* part, int n_tile, int jcol, bool first) {
+  float v[32];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) {
+    const float x = valid ? __bfloat162float(__float2bfloat16(f[i])) : 0.f;
+    v[i] = x;
+    v[16 + i] = x * x;
+  }
+  const float tot = warp_reduce_scatter32(v, lane);
+  float* dst = part + (lane < 16 ? 0 : n_tile) + jcol + (lane & 15);
+  *dst = first ? tot : *dst + tot;
+}
+
 // named barrier over the 128 epilogue threads (id 1; id 0 is __syncthreads)
 __device__ __forceinline__ void epilogue_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
@@ -50,6 +69,18 @@ __device__ __forceinline__ void epilogue_stats_flush(const float* s_sums, float*
   for (int t = etid; t < 2 * n_tile; t += 128) {
     const int col = col_base + (t % n_tile);
     if (col < Cout_p) atomicAdd(stats + (t < n_tile ? 0 : Cout_p) + col, s_sums[t]);
+  }
+}
+
+// parts = [4 warps][2*n_tile]; one global atomic per channel and quantity per CTA.
+__device__ __forceinline__ void epilogue_stats_flush_parts(const float* parts, float* stats, int n_tile,
+                                                           int col_base, int Cout_p, int etid) {
+  epilogue_bar();
+  const int w = 2 * n_tile;
+  for (int t = etid; t < w; t += 128) {
+    const int col = col_base + (t % n_tile);
+    if (col < Cout_p)
+      atomicAdd(stats + (t < n_tile ? 0 : Cout_p) + col, parts[t] + parts[w + t] + parts[2 * w + t] + parts[3 * w + t]);
   }
 }
 
