@@ -94,7 +94,7 @@ class PyramidNet(nn.Module):
         x = self.bn1(self.conv1(self.input(x), stats_for=self.bn1), stats_for=self.layer1[0].bn1)
         x = self.layer3(self.layer2(self.layer1(x)))
         x = self.avgpool(self.bn_out(x, relu=True))
-        if not x.is_cuda:
+        if not L.is_native(x):
             x = x.flatten(1)
         return self.output(self.fc_out(x))
 

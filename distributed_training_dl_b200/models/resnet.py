@@ -101,7 +101,7 @@ class StemConv7x7s2(nn.Conv2d):
     s2d_weight = staticmethod(s2d_weight)
 
     def forward(self, x):
-        if not x.is_cuda:
+        if not L.is_native(x):
             return super().forward(x)
         return _StemFn.apply(x, self.weight, self._op)
 
@@ -161,7 +161,7 @@ class ResNet50(nn.Module):
         x = self.maxpool(self.bn1(self.conv1(x), relu=True))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = self.avgpool(x)
-        if not x.is_cuda:
+        if not L.is_native(x):
             x = x.flatten(1)
         return self.output(self.fc(x))
 
