@@ -18,6 +18,7 @@ bucket logic over ``torch.distributed`` collectives.
 from __future__ import annotations
 
 import os
+import time
 
 import torch
 import torch.distributed as dist
@@ -61,6 +62,10 @@ class Reducer:
         self._works = []
         self._launched_any = False
         self._callback_queued = False
+        # per-bucket timing of the collectives (eager steps only; DTDL_BUCKET_TIMING=1 or
+        # reducer.bucket_timing = True), read back with bucket_report()
+        self.bucket_timing = os.environ.get("DTDL_BUCKET_TIMING") == "1"
+        self._bucket_events = []
         self._hook = fn.add_ready_hook(self._on_ready)
         for p in self.arena.params:
             p.register_post_accumulate_grad_hook(self._torch_hook)
@@ -173,20 +178,32 @@ class Reducer:
                 ev = torch.cuda.Event()
                 ev.record(s)
                 self.comm_stream.wait_event(ev)
+            timed = self.bucket_timing and not torch.cuda.is_current_stream_capturing()
+            if timed:
+                e0 = torch.cuda.Event(enable_timing=True)
+                e0.record(self.comm_stream)
+            two = self.peer.choose_two_shot(n * 4)
             if self._fused():
                 opt = self.optimizer
                 m = opt._state_flat[opt.state_names[0]]
                 v = opt._state_flat[opt.state_names[1]] if len(opt.state_names) > 1 else None
-                two = self.peer.choose_two_shot(n * 4)
                 self.state_sharded = self.state_sharded or bool(two)
                 self.peer.reduce_update(a.grad_buf, a.param_buf, m, v, opt._hyper_dev, off_b, n,
                                         opt.opt_code, two_shot=two, stream=self.comm_stream)
             else:
                 self.peer.allreduce(a.grad_buf, off_b, n, scale=1.0 / self.world, stream=self.comm_stream)
+            if timed:
+                e1 = torch.cuda.Event(enable_timing=True)
+                e1.record(self.comm_stream)
+                # an in-place plain all-reduce never runs the one-shot schedule (peer.allreduce)
+                variant = "nvls" if two == 2 else ("two-shot" if (two == 1 or not self._fused()) else "one-shot")
+                kind = ("fused " if self._fused() else "") + variant
+                self._bucket_events.append((bucket, kind, e0, e1))
         elif self.world > 1:
             g = a.grad_flat[bucket.offset: bucket.offset + n]
+            t0 = time.perf_counter() if self.bucket_timing else None
             work = dist.all_reduce(g, group=self.comm.group, async_op=True)
-            self._works.append((work, bucket))
+            self._works.append((work, bucket, t0))
         self._launched_any = True
 
     def flush(self):
@@ -206,8 +223,10 @@ class Reducer:
             if getattr(self, "_user_stream", None) is not None:
                 self._user_stream.wait_stream(self.comm_stream)
         elif self.world > 1:
-            for work, bucket in self._works:
+            for work, bucket, t0 in self._works:
                 work.wait()
+                if t0 is not None:   # host clock from launch to completion: an upper bound
+                    self._bucket_events.append((bucket, self.backend, (time.perf_counter() - t0) * 1e3, None))
                 g = a.grad_flat[bucket.offset: bucket.offset + bucket.numel]
                 g.div_(self.world)
                 if fused:
@@ -220,6 +239,24 @@ class Reducer:
     def wait(self):
         """Makes reduced gradients visible to the current stream (non-fused use)."""
         self.finish_step(fused=False)
+
+    def bucket_report(self, clear=True):
+        """Per-bucket time and achieved bus bandwidth of the collectives timed since the last call
+        (SURVEY.md section 5.5).  Bus bandwidth = 2 (W-1)/W * bytes / time, the figure NCCL's
+        tests quote.  Peer back end: device time of the kernel on the communication stream
+        (includes waiting for the slowest rank); torch.distributed back ends: host clock."""
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+        rows = []
+        for bucket, kind, a0, a1 in self._bucket_events:
+            ms = a0.elapsed_time(a1) if a1 is not None else a0
+            nbytes = bucket.numel * 4
+            bus = 2.0 * (self.world - 1) / self.world * nbytes / (ms * 1e-3) / 1e9 if ms > 0 else float("inf")
+            rows.append({"bucket": bucket.index, "bytes": nbytes, "ms": ms, "bus_GBps": bus, "kind": kind,
+                         "world": self.world})
+        if clear:
+            self._bucket_events = []
+        return rows
 
 
 class DistributedModel(nn.Module):

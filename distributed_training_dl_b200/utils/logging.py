@@ -81,6 +81,25 @@ def format_elapsed(seconds: float) -> str:
     return str(datetime.timedelta(seconds=seconds))
 
 
+def format_bucket_report(rows) -> str:
+    """Table of ``Reducer.bucket_report()`` rows: per-bucket collective time and achieved bus
+    bandwidth, averaged over the steps that were timed (SURVEY.md section 5.5 asks for it next to
+    the reference's loss / accuracy line, pytorch/single_gpu.py:114-116)."""
+    agg = {}
+    for r in rows:
+        a = agg.setdefault(r["bucket"], {"bytes": r["bytes"], "kind": r["kind"], "world": r["world"], "ms": 0.0, "n": 0})
+        a["ms"] += r["ms"]
+        a["n"] += 1
+    lines = ["bucket |     bytes | variant        |    ms | bus GB/s"]
+    for b in sorted(agg):
+        a = agg[b]
+        ms = a["ms"] / max(a["n"], 1)
+        w = a["world"]
+        bus = 2.0 * (w - 1) / w * a["bytes"] / (ms * 1e-3) / 1e9 if ms > 0 else float("inf")
+        lines.append(f"{b:6d} | {a['bytes']:9d} | {a['kind']:14s} | {ms:5.3f} | {bus:8.1f}")
+    return "\n".join(lines)
+
+
 class JsonLog:
     """Append-only JSON log (Chainer ``LogReport``, chainer/train_mnist.py:96)."""
 

@@ -32,11 +32,17 @@ def main_worker(local_rank, args):
                               weight_decay=args.weight_decay)
     scheduler = torch.optim.lr_scheduler.StepLR(optimizer, step_size=2, gamma=0.1)
     step = dtdl.TrainStep(net, optimizer, dtdl.CrossEntropyLoss(), graph=not args.no_graph)
+    net.reducer.bucket_timing = args.bucket_timing    # eager (warm-up / --no-graph) steps are timed
     net.train()
     for epoch in range(1, args.epochs + 1):
         sampler.set_epoch(epoch)   # the reference never reshuffles between epochs
         train_epoch(epoch, step, loader, comm.device, args.log_interval, logger)
         scheduler.step()
+        if args.bucket_timing:
+            rows = net.reducer.bucket_report()
+            if rows:
+                logger.info("gradient buckets (collective time, achieved bus bandwidth):\n"
+                            + dtdl.utils.format_bucket_report(rows))
     if args.save_model:
         path = dtdl.save_model(net.module, os.path.join(args.train_dir, "distributed_data_parallel.pth"),
                                per_rank=True)
@@ -47,6 +53,8 @@ def main_worker(local_rank, args):
 def main():
     parser = pytorch_flags("B200-native CIFAR-10 training, one process per GPU", distributed=True)
     parser.add_argument("--spawn", type=int, default=0, help="start N local worker processes")
+    parser.add_argument("--bucket-timing", action="store_true",
+                        help="report per-bucket all-reduce time and bus bandwidth after each epoch")
     args = parser.parse_args()
     if args.spawn:
         dtdl.spawn(main_worker, nprocs=args.spawn, args=(args,))

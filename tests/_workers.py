@@ -41,6 +41,7 @@ def ddp_equivalence(i, world, init_kind, port, outdir):
         p.grad = None
     opt = dtdl.FusedSGD(net.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
     ropt = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-4)
+    net.reducer.bucket_timing = True      # per-bucket time / bus bandwidth report
     g = torch.Generator().manual_seed(7)
     for step in range(3):
         xs = torch.randn(world, 8, 784, generator=g)
@@ -54,7 +55,7 @@ def ddp_equivalence(i, world, init_kind, port, outdir):
             local = copy.deepcopy(ref)
             F.cross_entropy(local(xs[i]), ts[i]).backward()
             net.reducer.flush()
-            for work, bucket in net.reducer._works:
+            for work, bucket, _t0 in net.reducer._works:
                 work.wait()
             for (n_, p), q in zip(net.module.named_parameters(), local.parameters()):
                 mean = sum(_gather(comm, q.grad)) / world
@@ -71,6 +72,12 @@ def ddp_equivalence(i, world, init_kind, port, outdir):
     for p in net.parameters():
         allp = _gather(comm, p)
         assert all(torch.equal(allp[0], q) for q in allp)
+    rows = net.reducer.bucket_report()
+    assert len(rows) == 3 * len(net.reducer.arena.buckets)          # every bucket of every step
+    assert all(r["ms"] > 0 and r["bus_GBps"] > 0 and r["kind"] == "gloo" for r in rows)
+    assert sum(r["bytes"] for r in rows[:len(net.reducer.arena.buckets)]) == 4 * net.reducer.arena.numel
+    assert "bus" in dtdl.utils.format_bucket_report(rows)
+    assert net.reducer.bucket_report() == []
     # optimizer state in torch format
     sd = opt.state_dict()
     assert "momentum_buffer" in sd["state"][0]
