@@ -1,6 +1,13 @@
 // Epilogue helpers shared by the implicit-GEMM kernels: per-channel sum / sum-of-squares of the
 // tile that is being written (the statistics the following training-mode BatchNorm needs),
 // taken from the fp32 accumulators after rounding to the stored bf16 value.
+//
+// Inside the CTA nothing is atomic: every epilogue warp owns one row part[2*n_tile] of a scratch
+// area (the kernels lend their pipeline stage memory, idle once the accumulator is complete), and
+// lane L stores the warp total of column/quantity L.  (Shared-memory float atomics are
+// compare-and-swap loops; four warps hitting the same 32 words every chunk made them the
+// dominant cost of an earlier version.)  The flush adds the four rows and issues one global
+// atomic per channel and quantity per CTA.
 #pragma once
 #include "../common/ptx.cuh"
 
@@ -22,25 +29,8 @@ __device__ __forceinline__ float warp_reduce_scatter32(float (&v)[32], int lane)
   return v[0];
 }
 
-// One 16-column chunk of one warp's 32 rows -> shared accumulators s_sums[2][n_tile].
-__device__ __forceinline__ void epilogue_col_stats(const float (&f)[16], bool valid, int lane,
-                                                   float* s_sums, int n_tile, int jcol) {
-  float v[32];
-#pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    const float x = valid ? __bfloat162float(__float2bfloat16(f[i])) : 0.f;
-    v[i] = x;
-    v[16 + i] = x * x;
-  }
-  const float tot = warp_reduce_scatter32(v, lane);
-  atomicAdd(&s_sums[(lane < 16 ? 0 : n_tile) + jcol + (lane & 15)], tot);
-}
-
-// Atomic-free accumulation inside the CTA: every epilogue warp owns one row part[2*n_tile] of a
-// scratch area (the kernels lend their pipeline stage memory, idle once the accumulator is
-// complete); lane L writes the warp total of column/quantity L with a plain store.  Shared-memory
-// float atomics are compare-and-swap loops, and four warps hitting the same 32 words every chunk
-// made them the dominant cost of the statistics epilogue.
+// One 16-column chunk of one warp's 32 rows -> this warp's row of partial sums.  `first` is false
+// when the warp visits the same columns again (second sub-tile of the halo kernel).
 __device__ __forceinline__ void epilogue_col_stats_part(const float (&f)[16], bool valid, int lane,
                                                         float* part, int n_tile, int jcol, bool first) {
   float v[32];
@@ -58,21 +48,7 @@ __device__ __forceinline__ void epilogue_col_stats_part(const float (&f)[16], bo
 // named barrier over the 128 epilogue threads (id 1; id 0 is __syncthreads)
 __device__ __forceinline__ void epilogue_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
 
-__device__ __forceinline__ void epilogue_stats_init(float* s_sums, int n_tile, int etid) {
-  for (int t = etid; t < 2 * n_tile; t += 128) s_sums[t] = 0.f;
-  epilogue_bar();
-}
-
-__device__ __forceinline__ void epilogue_stats_flush(const float* s_sums, float* stats, int n_tile,
-                                                     int col_base, int Cout_p, int etid) {
-  epilogue_bar();
-  for (int t = etid; t < 2 * n_tile; t += 128) {
-    const int col = col_base + (t % n_tile);
-    if (col < Cout_p) atomicAdd(stats + (t < n_tile ? 0 : Cout_p) + col, s_sums[t]);
-  }
-}
-
-// parts = [4 warps][2*n_tile]; one global atomic per channel and quantity per CTA.
+// parts = [4 warps][2*n_tile]; stats = [2][Cout_p] in global memory (pre-zeroed by the caller).
 __device__ __forceinline__ void epilogue_stats_flush_parts(const float* parts, float* stats, int n_tile,
                                                            int col_base, int Cout_p, int etid) {
   epilogue_bar();
