@@ -256,6 +256,13 @@ def init(backend=None, init_method=None, rank=None, world_size=None, local_rank=
 def shutdown():
     global _current
     if _current is not None and _current.peer is not None:
+        if _current.size > 1 and dist.is_initialized():
+            # nobody unmaps memory a slower rank might still be touching
+            try:
+                torch.cuda.synchronize(_current.device)
+                dist.monitored_barrier(group=_current.control, timeout=datetime.timedelta(seconds=60))
+            except Exception:   # noqa: BLE001 - a peer that already died must not block our exit
+                pass
         _current.peer.close()
     _current = None
     if dist.is_initialized():
