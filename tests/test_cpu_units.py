@@ -215,3 +215,53 @@ def test_native_library_resolves_every_symbol():
     handle = ctypes.CDLL(nv.LIB_PATH, mode=ctypes.RTLD_GLOBAL | 2)   # 2 = RTLD_NOW
     for name in nv._parse_header(nv.HEADER_PATH):
         assert hasattr(handle, name), name
+
+
+def _bare_peer(world, use_nvls=False, nvls_min=0):
+    """A PeerComm without a GPU behind it: enough state for the pure policy methods."""
+    from distributed_training_dl_b200.parallel.peer import PeerComm
+    pc = object.__new__(PeerComm)
+    pc.rank, pc.world, pc.use_nvls, pc.nvls_min_bytes = 0, world, use_nvls, nvls_min
+    pc.two_shot_min_bytes = 256 * 1024
+    pc._local_group = None
+    return pc
+
+
+def test_collective_variant_policy(monkeypatch):
+    """one-shot below 256 KiB, two-shot above; multicast (2) for every size once NVLS is on;
+    the auto policy turns NVLS on from 4 ranks and the forced mode refuses a box without it."""
+    from distributed_training_dl_b200 import _native as nv
+    pc = _bare_peer(2)
+    assert pc.choose_two_shot(1024) == 0 and pc.choose_two_shot(1 << 20) == 1
+    assert _bare_peer(1).choose_two_shot(1 << 30) == 0          # a single rank never communicates
+    pn = _bare_peer(8, use_nvls=True)
+    assert pn.choose_two_shot(1024) == 2 and pn.choose_two_shot(1 << 28) == 2
+    pm = _bare_peer(8, use_nvls=True, nvls_min=1 << 20)
+    assert pm.choose_two_shot(1024) == 0 and pm.choose_two_shot(1 << 19) == 1 and pm.choose_two_shot(1 << 21) == 2
+
+    monkeypatch.delenv("DTDL_NVLS", raising=False)
+    for world, ok, want in [(2, True, False), (4, True, True), (8, True, True), (8, False, False)]:
+        p = _bare_peer(world)
+        p._decide_nvls(ok)
+        assert p.use_nvls is want, (world, ok)
+    monkeypatch.setenv("DTDL_NVLS", "1")
+    p = _bare_peer(2)
+    p._decide_nvls(True)
+    assert p.use_nvls is True                                     # forced on below the auto threshold
+    with pytest.raises(nv.NativeError):
+        _bare_peer(2)._decide_nvls(False)
+    monkeypatch.setenv("DTDL_NVLS", "0")
+    p = _bare_peer(8)
+    p._decide_nvls(True)
+    assert p.use_nvls is False
+
+
+def test_bucket_report_formatting():
+    from distributed_training_dl_b200.utils import format_bucket_report
+    rows = [{"bucket": 0, "bytes": 1 << 20, "ms": 0.02, "bus_GBps": 0.0, "kind": "fused nvls", "world": 8},
+            {"bucket": 1, "bytes": 25 << 20, "ms": 0.10, "bus_GBps": 0.0, "kind": "fused nvls", "world": 8},
+            {"bucket": 0, "bytes": 1 << 20, "ms": 0.04, "bus_GBps": 0.0, "kind": "fused nvls", "world": 8}]
+    text = format_bucket_report(rows).splitlines()
+    assert len(text) == 3 and "bus GB/s" in text[0]
+    # bucket 0: mean of 0.02 and 0.04 ms -> 2*(7/8)*1 MiB / 0.03 ms = 61.2 GB/s
+    assert abs(float(text[1].split("|")[-1]) - 2 * 7 / 8 * (1 << 20) / 0.03e-3 / 1e9) < 0.1
