@@ -1,0 +1,64 @@
+"""Regenerates profiles/sass/: per-kernel SASS listings of the hot kernels and the instruction-count
+table (UTCHMMA = tcgen05.mma, UTMALDG = TMA tensor load, LDTM = tcgen05.ld, LDGMC = multimem.ld_reduce).
+Runs on the build machine: cuobjdump needs no GPU.
+
+    python tools/sass_table.py
+"""
+import os
+import re
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "distributed_training_dl_b200", "lib", "libdtdl_b200.so")
+OUT = os.path.join(ROOT, "profiles", "sass")
+
+COLUMNS = [("UTCHMMA", r"\bUTCHMMA"), ("UTMALDG", r"\bUTMALDG"), ("LDTM", r"\bLDTM"),
+           ("UTC barrier/alloc", r"\bUTCBAR|\bUTCATOMSWS|\bUTCCP"), ("SYNCS", r"\bSYNCS"), ("HMMA", r"\bHMMA"),
+           ("LDG", r"\bLDG\b|\bLDG\."), ("LDGMC", r"\bLDGMC"), ("STG", r"\bSTG"), ("RED/ATOM", r"\bRED\b|\bRED\.|\bATOM"),
+           ("SHFL", r"\bSHFL"), ("MEMBAR", r"\bMEMBAR")]
+LISTINGS = {"conv_gemm_kernel": "conv_gemm.sass", "conv_gemm_v2_kernel": "conv_gemm_v2.sass",
+            "conv_wgrad_kernel": "conv_wgrad.sass", "bn_apply_kernel": "bn_apply.sass",
+            "bn_apply_stats_kernel": "bn_apply_stats.sass", "bn_bwd_apply_kernel": "bn_bwd_apply.sass",
+            "softmax_ce_kernel": "softmax_ce.sass", "broadcast_kernel": "broadcast.sass",
+            "reduce_kernelILi8E": "reduce_fused.sass", "nvls_reduce_kernel": "nvls_reduce.sass",
+            "pack_weights_kernel": "pack_weights.sass"}
+
+
+def main():
+    if not os.path.exists(LIB):
+        sys.exit("build the library first (./build.sh)")
+    text = subprocess.run(["cuobjdump", "-sass", LIB], capture_output=True, text=True, check=True).stdout
+    parts = re.split(r"(?=^\s*Function : )", text, flags=re.M)
+    os.makedirs(OUT, exist_ok=True)
+    rows = []
+    for part in parts:
+        m = re.match(r"\s*Function : (\S+)", part)
+        if not m:
+            continue
+        name = m.group(1)
+        code = [ln for ln in part.splitlines() if re.search(r"/\*[0-9a-f]{4}\*/", ln)]
+        counts = [sum(1 for ln in code if re.search(rx, ln)) for _, rx in COLUMNS]
+        rows.append((name, len(code), counts))
+        for key, fname in LISTINGS.items():
+            if key in name:
+                with open(os.path.join(OUT, fname), "w") as f:
+                    f.write(part)
+    rows.sort(key=lambda r: (-r[2][0], -r[2][1], r[0]))
+    with open(os.path.join(OUT, "README.md"), "w") as f:
+        f.write("# SASS evidence (`cuobjdump -sass` of libdtdl_b200.so, sm_100a; regenerate with `python tools/sass_table.py`)\n\n")
+        f.write("Instruction counts per kernel.  `UTCHMMA` = tcgen05.mma, `UTMALDG` = TMA tensor load, `LDTM` = "
+                "tcgen05.ld, `SYNCS` = mbarrier operations, `LDGMC` = multimem.ld_reduce (in-switch reduction; the "
+                "matching multimem.st is an `STG.E.128.STRONG.SYS` to the multicast address).  No `HMMA` (legacy "
+                "mma.sync) anywhere.  The collective kernels dereference peer pointers with plain `LDG`/`STG` (peer "
+                "memory is mapped into the address space) plus `.SYS`-scope flag loads and stores.  Full listings "
+                "of the main kernels are next to this file.\n\n")
+        f.write("| kernel | instrs | " + " | ".join(c for c, _ in COLUMNS) + " |\n")
+        f.write("|---|---|" + "---|" * len(COLUMNS) + "\n")
+        for name, n, counts in rows:
+            f.write(f"| `{name}` | {n} | " + " | ".join(str(c) for c in counts) + " |\n")
+    print(f"{len(rows)} kernels -> {OUT}/README.md")
+
+
+if __name__ == "__main__":
+    main()
