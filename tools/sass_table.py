@@ -15,7 +15,7 @@ OUT = os.path.join(ROOT, "profiles", "sass")
 
 COLUMNS = [("UTCHMMA", r"\bUTCHMMA"), ("UTMALDG", r"\bUTMALDG"), ("LDTM", r"\bLDTM"),
            ("UTC barrier/alloc", r"\bUTCBAR|\bUTCATOMSWS|\bUTCCP"), ("SYNCS", r"\bSYNCS"), ("HMMA", r"\bHMMA"),
-           ("LDG", r"\bLDG\b|\bLDG\."), ("LDGMC", r"\bLDGMC"), ("STG", r"\bSTG"), ("RED/ATOM", r"\bRED\b|\bRED\.|\bATOM"),
+           ("LDG", r"\bLDG\b|\bLDG\."), ("LDGMC", r"\bLDGMC"), ("STG", r"\bSTG"), ("RED/ATOM", r"\bREDG?\b|\bREDG?\.|\bATOM"),
            ("SHFL", r"\bSHFL"), ("MEMBAR", r"\bMEMBAR")]
 LISTINGS = {"conv_gemm_kernel": "conv_gemm.sass", "conv_gemm_v2_kernel": "conv_gemm_v2.sass",
             "conv_wgrad_kernel": "conv_wgrad.sass", "bn_apply_kernel": "bn_apply.sass",
