@@ -86,3 +86,96 @@ class SyntheticDataset(Dataset):
 
     def __getitem__(self, i):
         return self.x[i], self.y[i]
+
+
+class PinnedPrefetcher:
+    """Feeds ``(input, target)`` batches to a training step through a ring of reusable page-locked
+    buffers filled by a background thread (the real-data input path: pytorch/single_gpu.py:96-97
+    copies every batch from pageable memory, synchronously).
+
+    ``tensor.pin_memory()`` per batch allocates page-locked memory every step; here ``depth``
+    buffers per field are allocated once (re-allocated only if a batch is larger than any before)
+    and the copy into them overlaps the previous step.  A slot is refilled only after the work
+    the consumer enqueued while it held that slot has finished on the GPU: when the consumer asks
+    for the next batch, an event is recorded on its current stream and the worker waits for it
+    (on its own thread) before overwriting the slot.  Without CUDA the buffers are ordinary
+    memory and there is nothing to wait for.
+
+        for x, t in PinnedPrefetcher(loader):
+            loss = step(x, t)          # TrainStep copies x, t to the device asynchronously
+    """
+
+    def __init__(self, loader, depth: int = 3, device=None):
+        import queue
+        import threading
+        if depth < 2:
+            raise ValueError("depth must be at least 2 (one slot in use, one being filled)")
+        self.loader, self.depth = loader, depth
+        self.cuda = torch.cuda.is_available()
+        self.device = device
+        self._queue_mod, self._threading = queue, threading
+        self._slots = [{"bufs": None, "event": None} for _ in range(depth)]
+
+    def __len__(self):
+        return len(self.loader)
+
+    def _stage(self, slot, batch):
+        """Copies the fields of ``batch`` into the slot's buffers; returns views of the right size."""
+        fields = list(batch) if isinstance(batch, (tuple, list)) else [batch]
+        if slot["bufs"] is None:
+            slot["bufs"] = [None] * len(fields)
+        views = []
+        for i, f in enumerate(fields):
+            f = torch.as_tensor(f)
+            buf = slot["bufs"][i]
+            if buf is None or buf.dtype != f.dtype or buf.numel() < f.numel():
+                buf = torch.empty(f.numel(), dtype=f.dtype, pin_memory=self.cuda)
+                slot["bufs"][i] = buf
+            view = buf[: f.numel()].view(f.shape)
+            view.copy_(f)
+            views.append(view)
+        return tuple(views)
+
+    def _worker(self, free_q, ready_q, stop):
+        try:
+            for batch in self.loader:
+                idx = free_q.get()
+                if stop.is_set():
+                    return
+                slot = self._slots[idx]
+                if slot["event"] is not None:
+                    slot["event"].synchronize()     # the consumer's copies out of this slot are done
+                    slot["event"] = None
+                ready_q.put((idx, self._stage(slot, batch)))
+            ready_q.put((None, None))
+        except BaseException as e:  # noqa: BLE001 - surfaces in the consumer thread
+            ready_q.put((None, e))
+
+    def __iter__(self):
+        free_q, ready_q = self._queue_mod.Queue(), self._queue_mod.Queue()
+        for i in range(self.depth):
+            free_q.put(i)
+        stop = self._threading.Event()
+        t = self._threading.Thread(target=self._worker, args=(free_q, ready_q, stop), daemon=True)
+        t.start()
+        held = None
+        try:
+            while True:
+                idx, item = ready_q.get()
+                if held is not None:
+                    # everything the consumer enqueued for the previous batch is in its stream now
+                    if self.cuda:
+                        ev = torch.cuda.Event()
+                        ev.record(torch.cuda.current_stream(self.device))
+                        self._slots[held]["event"] = ev
+                    free_q.put(held)
+                    held = None
+                if idx is None:
+                    if isinstance(item, BaseException):
+                        raise item
+                    return
+                held = idx
+                yield item
+        finally:
+            stop.set()
+            free_q.put(0)       # wake the worker if it is waiting for a slot

@@ -61,10 +61,11 @@ def train_epoch(epoch, step, loader, device, log_interval, logger, rank_prefix=T
     meter = dtdl.utils.TrainMeter(device)
     epoch_start = time.time()
     n = len(loader)
-    for batch_idx, (inputs, targets) in enumerate(loader):
+    # batches reach the step through a ring of reusable page-locked buffers filled by a background
+    # thread, so the host-to-device copy is asynchronous and nothing is pinned per step
+    feed = dtdl.utils.PinnedPrefetcher(loader, device=device) if device.type == "cuda" else loader
+    for batch_idx, (inputs, targets) in enumerate(feed):
         start = time.time()
-        if device.type == "cuda":
-            inputs, targets = inputs.pin_memory(), targets.pin_memory()
         out = step(inputs, targets)
         stats = out if out.numel() == 2 else step.last_stats
         meter.update(stats[0], targets=targets, correct=stats[1])

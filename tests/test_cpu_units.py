@@ -265,3 +265,33 @@ def test_bucket_report_formatting():
     assert len(text) == 3 and "bus GB/s" in text[0]
     # bucket 0: mean of 0.02 and 0.04 ms -> 2*(7/8)*1 MiB / 0.03 ms = 61.2 GB/s
     assert abs(float(text[1].split("|")[-1]) - 2 * 7 / 8 * (1 << 20) / 0.03e-3 / 1e9) < 0.1
+
+
+def test_pinned_prefetcher_order_reuse_and_errors():
+    """Batches arrive in order and intact, the staging buffers are a fixed ring, a smaller last
+    batch fits the same buffers, loader errors surface in the consumer, early exit does not hang."""
+    from distributed_training_dl_b200.utils import PinnedPrefetcher
+    g = torch.Generator().manual_seed(0)
+    batches = [(torch.randn(8 if i < 9 else 3, 4, generator=g), torch.arange(8 if i < 9 else 3) + i) for i in range(10)]
+    ptrs, got = set(), []
+    for x, t in PinnedPrefetcher(batches, depth=3):
+        ptrs.add(x.data_ptr())
+        got.append((x.clone(), t.clone()))
+    assert len(got) == 10 and len(ptrs) <= 3
+    for (x, t), (rx, rt) in zip(got, batches):
+        assert torch.equal(x, rx) and torch.equal(t, rt)
+    assert len(PinnedPrefetcher(batches)) == 10
+
+    def broken():
+        yield batches[0]
+        raise RuntimeError("disk on fire")
+
+    it = iter(PinnedPrefetcher(broken(), depth=2))
+    next(it)
+    with pytest.raises(RuntimeError, match="disk on fire"):
+        next(it)
+    for i, _ in enumerate(PinnedPrefetcher(batches, depth=2)):     # leaving early must not block
+        if i == 2:
+            break
+    with pytest.raises(ValueError):
+        PinnedPrefetcher(batches, depth=1)

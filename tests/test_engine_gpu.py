@@ -93,3 +93,24 @@ def _stock_forward(model, x):
         return model(x)
     finally:
         L.is_native = orig
+
+
+def test_pinned_prefetcher_feeds_async_copies():
+    """Page-locked ring + event hand-back: 40 batches copied to the device with non_blocking copies
+    while the worker keeps refilling the same three buffers -- every device batch must be intact."""
+    from distributed_training_dl_b200.utils import PinnedPrefetcher
+    g = torch.Generator().manual_seed(1)
+    batches = [(torch.randn(64, 3, 32, 32, generator=g), torch.randint(0, 10, (64,), generator=g)) for _ in range(40)]
+    dev_x = torch.empty(40, 64, 3, 32, 32, device="cuda")
+    dev_t = torch.empty(40, 64, dtype=torch.long, device="cuda")
+    ptrs = set()
+    for i, (x, t) in enumerate(PinnedPrefetcher(batches, depth=3)):
+        assert x.is_pinned() and t.is_pinned()
+        ptrs.add(x.data_ptr())
+        torch.cuda._sleep(2_000_000)                 # keep the stream busy so copies really lag the host
+        dev_x[i].copy_(x, non_blocking=True)
+        dev_t[i].copy_(t, non_blocking=True)
+    torch.cuda.synchronize()
+    assert len(ptrs) <= 3
+    for i, (x, t) in enumerate(batches):
+        assert torch.equal(dev_x[i].cpu(), x) and torch.equal(dev_t[i].cpu(), t), i
