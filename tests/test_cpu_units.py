@@ -295,3 +295,62 @@ def test_pinned_prefetcher_order_reuse_and_errors():
             break
     with pytest.raises(ValueError):
         PinnedPrefetcher(batches, depth=1)
+
+
+def _write_idx(path, arr):
+    import gzip
+    import struct
+    with gzip.open(path, "wb") as f:
+        f.write(struct.pack(">HBB", 0, 0x08, arr.ndim) + struct.pack(">" + "I" * arr.ndim, *arr.shape))
+        f.write(arr.astype("uint8").tobytes())
+
+
+def test_mnist_idx_files_npz_cache_and_preprocessing(tmp_path):
+    """The reference's chainer/mnist_dataset.py + mnist_helper.py: four idx-gz files -> mnist.npz
+    cache -> (float32 image scaled to [0, scale], int label) pairs, flat or 1x28x28."""
+    import numpy as np
+    from distributed_training_dl_b200.utils import mnist
+    rng = np.random.default_rng(0)
+    xtr, ytr = rng.integers(0, 256, (20, 28, 28)), rng.integers(0, 10, 20)
+    xte, yte = rng.integers(0, 256, (7, 28, 28)), rng.integers(0, 10, 7)
+    for key, arr in (("train_x", xtr), ("train_y", ytr), ("test_x", xte), ("test_y", yte)):
+        _write_idx(str(tmp_path / mnist.FILES[key]), arr)
+    assert np.array_equal(mnist.read_idx(str(tmp_path / mnist.FILES["train_x"])), xtr.astype("uint8"))
+    (a, b), (c, d) = mnist.load_mnist(str(tmp_path), synthetic=False)
+    assert (tmp_path / "mnist.npz").exists()                       # cache written on first load
+    assert a.shape == (20, 28, 28) and np.array_equal(b, ytr) and np.array_equal(c, xte) and len(d) == 7
+    for key in mnist.FILES:                                        # second load needs only the cache
+        (tmp_path / mnist.FILES[key]).unlink()
+    train, test = mnist.get_mnist(str(tmp_path), ndim=1, scale=1.0, synthetic=False)
+    x0, y0 = train[0]
+    assert x0.shape == (784,) and x0.dtype == np.float32 and 0.0 <= x0.min() and x0.max() <= 1.0
+    assert np.allclose(x0, xtr[0].reshape(-1) / 255.0) and int(y0) == int(ytr[0]) and len(test) == 7
+    train3, _ = mnist.get_mnist(str(tmp_path), ndim=3, scale=255.0, synthetic=False)
+    assert train3[0][0].shape == (1, 28, 28) and np.allclose(train3[0][0][0], xtr[0])
+    with pytest.raises(FileNotFoundError):
+        mnist.load_mnist(str(tmp_path / "nothing_here"), synthetic=False)
+    (st, _), _ = mnist.load_mnist(str(tmp_path / "nothing_here"), synthetic=True)   # no network: random data
+    assert st.shape[1:] == (28, 28)
+    bad = tmp_path / "bad.gz"
+    import gzip
+    with gzip.open(bad, "wb") as f:
+        f.write(b"\\x00\\x00\\x0d\\x01" + b"\\x00" * 8)
+    with pytest.raises(ValueError):
+        mnist.read_idx(str(bad))
+
+
+def test_train_meter_log_line_and_rank_prefix(capsys):
+    """The reference's only observable output (pytorch/single_gpu.py:114-116 and the
+    'From Rank: r,' prefix of pytorch/distributed_data_parallel.py:144-148)."""
+    from distributed_training_dl_b200.utils import RankLogger, TrainMeter
+    m = TrainMeter("cpu")
+    logits = torch.tensor([[2.0, 0.0], [0.0, 3.0], [1.0, 0.0], [0.0, 1.0]])
+    targets = torch.tensor([0, 1, 1, 1])
+    m.update(torch.tensor(0.5), outputs=logits, targets=targets)
+    m.update(torch.tensor(1.5), targets=targets, correct=torch.tensor(4.0))
+    loss, acc = m.summary()
+    assert abs(loss - 1.0) < 1e-6 and abs(acc - 100.0 * 7 / 8) < 1e-4
+    line = m.line(3, 20, 782, 0.0123)
+    assert line.startswith("Epoch:[3][20/782]| loss: 1.000 | acc: 87.500 | batch time: 0.012s")
+    RankLogger().info("hello")
+    assert "hello" in capsys.readouterr().out
