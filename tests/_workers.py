@@ -147,3 +147,24 @@ def fd_channel(i, world, port, outdir):
     chan.close()
     open(os.path.join(outdir, f"ok_{i}"), "w").write("ok")
     dtdl.shutdown()
+
+
+def slurm_and_hosts_init(i, world, port, outdir, kind):
+    """init() from srun's environment, or from a TF_CONFIG-style host list."""
+    import distributed_training_dl_b200 as dtdl
+    for k in ("RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "LOCAL_RANK"):
+        os.environ.pop(k, None)
+    if kind == "slurm":
+        os.environ.update(SLURM_PROCID=str(i), SLURM_NTASKS=str(world), SLURM_LOCALID=str(i),
+                          SLURM_JOB_NODELIST="127.0.0.1", MASTER_PORT=str(port))
+        comm = dtdl.init(backend="gloo")
+    else:
+        hosts = ",".join(f"127.0.0.1:{port + r}" for r in range(world))
+        comm = dtdl.init(backend="gloo", worker_hosts=hosts, task_index=i)
+    assert (comm.rank, comm.size, comm.intra_rank) == (i, world, i)
+    got = comm.allgather_object(("rank", i))
+    assert got == [("rank", r) for r in range(world)]
+    assert abs(comm.allreduce_mean(float(i)) - (world - 1) / 2.0) < 1e-6
+    comm.barrier()
+    open(os.path.join(outdir, f"ok_{i}"), "w").write("ok")
+    dtdl.shutdown()

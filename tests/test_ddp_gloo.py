@@ -6,7 +6,7 @@ import pytest
 import distributed_training_dl_b200 as dtdl
 from distributed_training_dl_b200.utils import free_port
 
-from _workers import ddp_equivalence, ddp_pyramidnet, fd_channel
+from _workers import ddp_equivalence, ddp_pyramidnet, fd_channel, slurm_and_hosts_init
 
 
 @pytest.mark.parametrize("init_kind", ["tcp", "env"])
@@ -27,4 +27,11 @@ def test_ddp_pyramidnet_gloo(tmp_path):
 def test_fd_channel(tmp_path, world):
     """The descriptor all-gather that carries cuMem / multicast handles between ranks."""
     dtdl.spawn(fd_channel, nprocs=world, args=(world, free_port(), str(tmp_path)), set_env=False)
+    assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
+
+
+@pytest.mark.parametrize("kind", ["slurm", "hosts"])
+def test_init_from_slurm_env_and_host_list(tmp_path, kind):
+    world = 2
+    dtdl.spawn(slurm_and_hosts_init, nprocs=world, args=(world, free_port(), str(tmp_path), kind), set_env=False)
     assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
