@@ -58,6 +58,33 @@ def main():
         for name, n, counts in rows:
             f.write(f"| `{name}` | {n} | " + " | ".join(str(c) for c in counts) + " |\n")
     print(f"{len(rows)} kernels -> {OUT}/README.md")
+    ptxas_table()
+
+
+def ptxas_table():
+    """`-Xptxas -v` of the last build (build/*.log): registers, spills, static shared memory."""
+    import glob
+    pat = re.compile(r"Compiling entry function '(\S+)' for 'sm_100a'\nptxas info\s+: Function properties for \S+\n"
+                     r"\s+(\d+) bytes stack frame, (\d+) bytes spill stores, (\d+) bytes spill loads\n"
+                     r"ptxas info\s+: Used (\d+) registers, used (\d+) barriers"
+                     r"(?:, (\d+) bytes cumulative stack size)?(?:, (\d+) bytes smem)?")
+    rows = []
+    for log in sorted(glob.glob(os.path.join(ROOT, "build", "*.log"))):
+        src = os.path.basename(log).replace(".o.log", "").replace("csrc_", "").replace("_", "/", 1)
+        for m in pat.finditer(open(log).read()):
+            name, stack, sst, sld, regs, bars, _cum, smem = m.groups()
+            rows.append((src, name, int(regs), int(stack), int(sst), int(sld), int(bars), int(smem or 0)))
+    if not rows:
+        print("no build logs (run ./build.sh first): ptxas table not written")
+        return
+    with open(os.path.join(OUT, "ptxas.md"), "w") as f:
+        f.write("# `-Xptxas -v` per kernel (sm_100a, `./build.sh`; regenerate with `python tools/sass_table.py`)\n\n")
+        f.write("Dynamic shared memory (pipeline stages, up to 224 KB) is chosen at launch and not listed here.\n\n")
+        f.write("| source | kernel | registers | stack B | spill st B | spill ld B | barriers | static smem B |\n")
+        f.write("|---|---|---|---|---|---|---|---|\n")
+        for r in sorted(rows, key=lambda r: (r[0], -r[2])):
+            f.write(f"| {r[0]} | `{r[1]}` | {r[2]} | {r[3]} | {r[4]} | {r[5]} | {r[6]} | {r[7]} |\n")
+    print(f"{len(rows)} kernels -> {OUT}/ptxas.md")
 
 
 if __name__ == "__main__":
