@@ -215,10 +215,19 @@ __global__ void bn_apply_kernel(const BnApplyArgs a) {
   bn_apply_prologue(a, sc, sh);
 
   const long long total = a.P * a.G;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int g = (int)(i % a.G);
-    const long long p = i / a.G;
+  // (g, p) = (i % G, i / G) follow i by carry arithmetic: a 64-bit division per element is a
+  // subroutine call of several dozen instructions, more than the rest of the loop body
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  int g = (int)(i % a.G);
+  long long p = i / a.G;
+  const int dg = (int)(stride % a.G);
+  const long long dp = stride / a.G;
+  for (; i < total; i += stride, g += dg, p += dp) {
+    if (g >= a.G) {
+      g -= a.G;
+      ++p;
+    }
     F8 f = unpack8(a.x[i]);
 #pragma unroll
     for (int k = 0; k < 8; ++k) f.v[k] = f.v[k] * sc[g * 8 + k] + sh[g * 8 + k];
@@ -408,10 +417,17 @@ __global__ void bn_bwd_apply_kernel(const BnBwdArgs a) {
     for (int i = threadIdx.x; i < a.zero_n; i += blockDim.x) a.zero_buf[i] = 0.f;
   __syncthreads();
   const long long total = a.P * a.G;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int g = (int)(i % a.G);
-    const long long p = i / a.G;
+  const long long stride = (long long)gridDim.x * blockDim.x;   // carry arithmetic, see bn_apply_kernel
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  int g = (int)(i % a.G);
+  long long p = i / a.G;
+  const int dg = (int)(stride % a.G);
+  const long long dp = stride / a.G;
+  for (; i < total; i += stride, g += dg, p += dp) {
+    if (g >= a.G) {
+      g -= a.G;
+      ++p;
+    }
     F8 d = unpack8(a.dy[i]);
     const F8 xv = unpack8(a.x[i]);
     if (a.relu) {
