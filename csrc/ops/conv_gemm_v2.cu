@@ -1,5 +1,7 @@
 // Implicit-GEMM convolution forward / data-gradient, second generation: shared-memory reuse
-// across filter rows and across two pixel sub-tiles.
+// across filter rows and across two pixel sub-tiles.  Same capability as conv_gemm.cu (K-O1 / K-O3
+// of SURVEY.md 2.5: the 3x3 convolutions of pytorch/model.py:28-32,62-63 and their data gradients,
+// which the reference gets from cuDNN), for the 32- and 16-pixel-wide stages.
 //
 // The first-generation kernel (conv_gemm.cu) loads one shifted activation box per filter tap,
 // i.e. the same pixels travel L2 -> shared memory KH*KW times, and every 128-pixel tile

@@ -1,6 +1,8 @@
 // Epilogue helpers shared by the implicit-GEMM kernels: per-channel sum / sum-of-squares of the
 // tile that is being written (the statistics the following training-mode BatchNorm needs),
-// taken from the fp32 accumulators after rounding to the stored bf16 value.
+// taken from the fp32 accumulators after rounding to the stored bf16 value.  This is the
+// "statistics reduction fused into the producer conv epilogue" of SURVEY.md 2.5 K-O5; the
+// reference runs a separate BatchNorm kernel after every convolution (pytorch/model.py:41-46).
 //
 // Inside the CTA nothing is atomic: every epilogue warp owns one row part[2*n_tile] of a scratch
 // area (the kernels lend their pipeline stage memory, idle once the accumulator is complete), and

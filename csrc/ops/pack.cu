@@ -1,6 +1,8 @@
 // fp32 master weights (torch OIHW / [out,in]) -> bf16 operand packs for the
 // tcgen05 kernels, for a whole model in ONE launch (a device-side table lists
-// the layers).  Runs once per optimizer step, right after the update.
+// the layers).  Runs once per optimizer step, right after the update.  (No counterpart in the
+// reference: cuDNN reads torch's OIHW fp32 weights directly, pytorch/model.py:28-32.  The packs
+// are what lets the TMA-fed tcgen05 kernels take K-major bf16 operands without a transform.)
 //
 //   fprop pack  wf[co][t][ci]   co < Cout_p16, ci < Cin_p   : w[co][ci][t]
 //   dgrad pack  wd[ci][t'][co]  ci < Cin_p16, co < Cout_p   : w[co][ci][taps-1-t']

@@ -5,6 +5,13 @@ Activation layout on the GPU: NHWC bf16, channel count padded to a multiple of 8
 Parameter gradients are written by the kernels straight into the parameter's
 gradient buffer (a view of the reducer's flat arena when the model is wrapped),
 so autograd never materialises or accumulates a weight gradient itself.
+
+What the reference gets from torch.nn / cuDNN and where it is here (SURVEY.md 2.5 b):
+``nn.Conv2d`` + its autograd (pytorch/model.py:28-32,62-63) -> ``_Conv``; ``nn.BatchNorm2d`` +
+``nn.ReLU`` + ``out += shortcut`` with the zero-padded identity (pytorch/model.py:27-50) ->
+``_BatchNorm``; ``nn.AvgPool2d`` (pytorch/model.py:11,76), Keras ``MaxPooling2D``
+(tensorflow2/mnist_single.py:19,21) -> ``_Pool`` / ``_GlobalAvgPool``; ``nn.CrossEntropyLoss`` and the
+argmax / eq / sum accuracy arithmetic (pytorch/single_gpu.py:99,105-108) -> ``_SoftmaxCE``.
 """
 from __future__ import annotations
 

@@ -1,4 +1,7 @@
-"""Device timing: CUDA events on the launching stream, max over ranks (never wall clock)."""
+"""Device timing: CUDA events on the launching stream, max over ranks (never wall clock).
+
+(The reference times steps with ``time.time()`` around a loop whose ``.item()`` calls happen to
+synchronise the device: pytorch/single_gpu.py:92-94,105-112.  Here timing is explicit.)"""
 from __future__ import annotations
 
 import os
