@@ -29,8 +29,9 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 
-int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
-                     const uint64_t* strides_bytes, const uint32_t* box) {
+int encode_tmap_act(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                    const uint64_t* strides_bytes, const uint32_t* box, int act, bool mn_major32,
+                    const uint32_t* elem_strides) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) {
     set_last_error("cuTensorMapEncodeTiled is not available from this driver");
@@ -43,16 +44,19 @@ int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_
   for (int i = 0; i < rank; ++i) {
     gdim[i] = dims[i];
     bdim[i] = box[i];
-    estr[i] = 1;
+    estr[i] = elem_strides ? elem_strides[i] : 1;
   }
   for (int i = 0; i + 1 < rank; ++i) gstr[i] = strides_bytes[i];
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base),
-                  gdim, gstr, bdim, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+  const CUtensorMapDataType dt =
+      act == kActF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  const CUtensorMapSwizzle sw = (act == kActF32 && mn_major32) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B
+                                                               : CU_TENSOR_MAP_SWIZZLE_128B;
+  CUresult r = fn(out, dt, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bdim, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     std::string m = "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r) +
-                    " rank=" + std::to_string(rank) + " dims=";
+                    " act=" + std::to_string(act) + " rank=" + std::to_string(rank) + " dims=";
     for (int i = 0; i < rank; ++i) m += std::to_string(dims[i]) + ",";
     m += " box=";
     for (int i = 0; i < rank; ++i) m += std::to_string(box[i]) + ",";
@@ -62,6 +66,11 @@ int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_
     return 1;
   }
   return 0;
+}
+
+int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                     const uint64_t* strides_bytes, const uint32_t* box) {
+  return encode_tmap_act(out, base, rank, dims, strides_bytes, box, kActBf16, false, nullptr);
 }
 
 int multicast_supported(int dev) {

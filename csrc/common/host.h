@@ -41,6 +41,20 @@ const char* get_last_error();
 int encode_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                      const uint64_t* strides_bytes, const uint32_t* box);
 
+// Activation storage types of the op kernels ("act" in the C ABI).
+enum { kActBf16 = 0, kActF32 = 1 };
+
+// Same for either activation type: act = kActBf16 -> bf16 elements, kActF32 -> fp32 elements (the
+// tensor core reads them as TF32).  `mn_major32` selects the 128-byte swizzle with 32-byte atoms
+// that tcgen05 requires for MN-major 32-bit operands (weight-gradient GEMM in fp32 mode); it is
+// ignored for bf16.  `elem_strides` (rank entries, may be null = all 1) lets a box sample every
+// other pixel (stride-2 convolutions).
+int encode_tmap_act(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
+                    const uint64_t* strides_bytes, const uint32_t* box, int act, bool mn_major32,
+                    const uint32_t* elem_strides = nullptr);
+
+static inline int act_esize(int act) { return act == kActF32 ? 4 : 2; }
+
 int sm_count();
 
 // 1 / 0 = the device can / cannot join an NVLS multicast object, -1 = query failed.

@@ -142,6 +142,29 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint6
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Same with fp32 operands read as TF32 (10-bit mantissa, the low 13 bits are ignored), fp32
+// accumulate: the precision cuDNN's default convolution path uses for fp32 tensors.  One
+// instruction covers K = 8 elements (32 bytes, as for bf16's K = 16).
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                          uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Activation storage type of a kernel instantiation: 0 = bf16 (kind::f16), 1 = fp32 (kind::tf32).
+template <int ACT>
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                     uint32_t accumulate) {
+  if (ACT == 0)
+    umma_bf16(tmem_d, adesc, bdesc, idesc, accumulate);
+  else
+    umma_tf32(tmem_d, adesc, bdesc, idesc, accumulate);
+}
 // mbarrier arrives once every MMA issued so far by this thread has retired.
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile(
@@ -171,14 +194,20 @@ __device__ __forceinline__ void tmem_ld_wait() {
 //             bytes apart; 64-element MN groups LBO bytes apart.
 // Bit layout follows the tcgen05 "matrix descriptor": start>>4 [0,14),
 // LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout [61,64) (2 = 128B).
+//
+// `layout` 2 = SWIZZLE_128B (16-byte swizzle atoms; every K-major operand and the bf16 MN-major
+// ones).  `layout` 1 = SWIZZLE_128B_BASE32B: the only layout tcgen05 accepts for MN-major 32-bit
+// (tf32) operands -- rows of 32 MN-elements (128 B) indexed by K, 32-byte chunks XOR-swizzled with
+// the row index modulo 4; 4-row K groups SBO bytes apart.  TMA writes it with
+// CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
 __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes,
-                                                   uint32_t sbo_bytes) {
+                                                   uint32_t sbo_bytes, uint32_t layout = 2) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
+  d |= (uint64_t)(layout & 7) << 61;
   return d;
 }
 
@@ -206,6 +235,25 @@ __host__ __device__ __forceinline__ uint32_t umma_idesc_bf16(int M, int N, int a
   d |= (uint32_t)((N >> 3) & 0x3F) << 17;
   d |= (uint32_t)((M >> 4) & 0x1F) << 24;
   return d;
+}
+
+// Instruction descriptor for kind::tf32 (fp32 storage read as TF32, fp32 D): a/b format 2.
+__host__ __device__ __forceinline__ uint32_t umma_idesc_tf32(int M, int N, int a_mn_major,
+                                                             int b_mn_major) {
+  uint32_t d = 0;
+  d |= 1u << 4;
+  d |= 2u << 7;
+  d |= 2u << 10;
+  d |= (uint32_t)(a_mn_major & 1) << 15;
+  d |= (uint32_t)(b_mn_major & 1) << 16;
+  d |= (uint32_t)((N >> 3) & 0x3F) << 17;
+  d |= (uint32_t)((M >> 4) & 0x1F) << 24;
+  return d;
+}
+template <int ACT>
+__host__ __device__ __forceinline__ uint32_t umma_idesc(int M, int N, int a_mn_major, int b_mn_major) {
+  return ACT == 0 ? umma_idesc_bf16(M, N, a_mn_major, b_mn_major)
+                  : umma_idesc_tf32(M, N, a_mn_major, b_mn_major);
 }
 
 // ----------------------------------------------------------------------------

@@ -29,6 +29,7 @@ namespace dtdl {
 struct ConvV2Args {
   int KH, KW, pad_h, pad_w;
   int chunks, last_slices, Cin_p;
+  int CB;              // channels per 128-byte row: 64 (bf16) or 32 (fp32 read as TF32)
   int BW, BH, MS;      // sub-tile = BW x BH = 128 pixels, MS sub-tiles per CTA
   int halo_rows;       // (MS*BH + KH - 1) * BW
   int tiles_h;
@@ -41,6 +42,7 @@ struct ConvV2Args {
   float* stats;
 };
 
+template <int ACT>
 __global__ void __launch_bounds__(256, 2)
 conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const ConvV2Args a) {
@@ -90,10 +92,10 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           uint8_t* st = smem + stage * a.stage_bytes;
           mbar_wait(&empty[stage], phase ^ 1, 21);
           mbar_arrive_expect_tx(&full[stage], tx);
-          tma_load_4d(st, &tmA, &full[stage], c * 64, s - a.pad_w, h0 - a.pad_h, n_img);
+          tma_load_4d(st, &tmA, &full[stage], c * a.CB, s - a.pad_w, h0 - a.pad_h, n_img);
           for (int r = 0; r < a.KH; ++r)
             tma_load_2d(st + a.a_stage_bytes + r * a.b_box_bytes, &tmB, &full[stage],
-                        (r * a.KW + s) * a.Cin_p + c * 64, nt * a.n_tile);
+                        (r * a.KW + s) * a.Cin_p + c * a.CB, nt * a.n_tile);
           if (++stage == a.stages) {
             stage = 0;
             phase ^= 1;
@@ -103,27 +105,27 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
   } else if (warp == 1) {
     if (elect_one()) {
-      const uint32_t idesc = umma_idesc_bf16(128, a.n_tile, 0, 0);
+      const uint32_t idesc = umma_idesc<ACT>(128, a.n_tile, 0, 0);
       const uint64_t desc0 = umma_smem_desc(smem_u32(smem), 16, 1024);
       const uint32_t row_bytes = (uint32_t)(a.BW * 128);          // one image row of the halo box
       const uint32_t sub_bytes = (uint32_t)(a.BH * a.BW * 128);   // one 128-pixel sub-tile
-      int stage = 0, phase = 0;
+      int stage = 0, phase = 0, c = 0;
       for (int g = 0; g < n_groups; ++g) {
-        const int c = g % a.chunks;
         mbar_wait(&full[stage], phase, 22);
         tc_fence_after();
         const int nsl = (c == a.chunks - 1) ? a.last_slices : 4;
+        if (++c == a.chunks) c = 0;
         const uint64_t sa = umma_desc_advance(desc0, (uint32_t)(stage * a.stage_bytes));
         const uint64_t sb = umma_desc_advance(sa, (uint32_t)a.a_stage_bytes);
         for (int m = 0; m < a.MS; ++m) {
           uint64_t ad = umma_desc_advance(sa, (uint32_t)(m * sub_bytes));
           uint64_t bd = sb;
           for (int r = 0; r < a.KH; ++r) {
-            umma_bf16(tmem_base + m * a.n_tile, ad, bd, idesc, (g > 0 || r > 0) ? 1u : 0u);
+            umma<ACT>(tmem_base + m * a.n_tile, ad, bd, idesc, (g > 0 || r > 0) ? 1u : 0u);
 #pragma unroll
             for (int k = 1; k < 4; ++k)
               if (k < nsl)
-                umma_bf16(tmem_base + m * a.n_tile, umma_desc_advance(ad, k * 32), umma_desc_advance(bd, k * 32), idesc, 1u);
+                umma<ACT>(tmem_base + m * a.n_tile, umma_desc_advance(ad, k * 32), umma_desc_advance(bd, k * 32), idesc, 1u);
             ad = umma_desc_advance(ad, row_bytes);
             bd = umma_desc_advance(bd, (uint32_t)a.b_box_bytes);
           }
@@ -142,7 +144,7 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int wo = row % a.BW;
     const int hi = row / a.BW;
     const bool relu = a.flags & 1;
-    const bool f32 = a.flags & 2;
+    const bool f32 = ACT == 1 || (a.flags & 2);
     // statistics scratch = the pipeline's stage memory (free once the accumulators are complete)
     float* s_parts = reinterpret_cast<float*>(smem);
     const int etid = threadIdx.x - 128;
@@ -166,30 +168,12 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           if (relu) f[i] = fmaxf(f[i], 0.f);
         }
         if (a.stats != nullptr)
-          epilogue_col_stats_part(f, valid, lane, s_parts + q * 2 * a.n_tile, a.n_tile, j * 16, m == 0);
+          epilogue_col_stats_part<ACT == 0>(f, valid, lane, s_parts + q * 2 * a.n_tile, a.n_tile, j * 16, m == 0);
         if (!valid) continue;
         if (f32) {
-          float* out = reinterpret_cast<float*>(a.y) + pix * a.Cout_p + col0;
-#pragma unroll
-          for (int i = 0; i < 16; ++i)
-            if (col0 + i < a.Cout_p) out[i] = f[i];
+          epilogue_store_f32(reinterpret_cast<float*>(a.y) + pix * a.Cout_p + col0, f, a.Cout_p - col0);
         } else {
-          __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(a.y) + pix * a.Cout_p + col0;
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            if (col0 + h * 8 < a.Cout_p) {
-              uint4 pk;
-              __nv_bfloat162 p0 = __floats2bfloat162_rn(f[h * 8 + 0], f[h * 8 + 1]);
-              __nv_bfloat162 p1 = __floats2bfloat162_rn(f[h * 8 + 2], f[h * 8 + 3]);
-              __nv_bfloat162 p2 = __floats2bfloat162_rn(f[h * 8 + 4], f[h * 8 + 5]);
-              __nv_bfloat162 p3 = __floats2bfloat162_rn(f[h * 8 + 6], f[h * 8 + 7]);
-              pk.x = *reinterpret_cast<uint32_t*>(&p0);
-              pk.y = *reinterpret_cast<uint32_t*>(&p1);
-              pk.z = *reinterpret_cast<uint32_t*>(&p2);
-              pk.w = *reinterpret_cast<uint32_t*>(&p3);
-              *reinterpret_cast<uint4*>(out + h * 8) = pk;
-            }
-          }
+          epilogue_store_bf16(reinterpret_cast<__nv_bfloat16*>(a.y) + pix * a.Cout_p + col0, f, a.Cout_p - col0);
         }
       }
     }
@@ -205,7 +189,8 @@ conv_gemm_v2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 // the per-tap kernel), >0 on error.
 int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, float* stats, int N,
                   int H, int W, int Cin_p, int Ho, int Wo, int Cout_p, int KH, int KW, int pad_h,
-                  int pad_w, int flags, cudaStream_t stream) {
+                  int pad_w, int flags, int act, cudaStream_t stream) {
+  const int esz = act_esize(act);
   if (Wo % 8 != 0 || Wo > 128 || 128 % Wo != 0) return -1;
   const int BW = Wo, BH = 128 / Wo;
   if (Ho < BH) return -1;
@@ -214,8 +199,9 @@ int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, 
   a.KW = KW;
   a.pad_h = pad_h;
   a.pad_w = pad_w;
-  a.chunks = (Cin_p + 63) / 64;
-  a.last_slices = (Cin_p - 64 * (a.chunks - 1) + 15) / 16;
+  a.CB = 128 / esz;
+  a.chunks = (Cin_p + a.CB - 1) / a.CB;
+  a.last_slices = ((Cin_p - a.CB * (a.chunks - 1)) * esz + 31) / 32;
   a.Cin_p = Cin_p;
   a.BW = BW;
   a.BH = BH;
@@ -270,28 +256,32 @@ int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, 
   CUtensorMap tmA, tmB;
   {
     uint64_t dims[4] = {(uint64_t)Cin_p, (uint64_t)W, (uint64_t)H, (uint64_t)N};
-    uint64_t str[3] = {(uint64_t)Cin_p * 2, (uint64_t)W * Cin_p * 2, (uint64_t)H * W * Cin_p * 2};
-    uint32_t box[4] = {64, (uint32_t)BW, (uint32_t)(MS * BH + KH - 1), 1};
-    if (encode_tmap_bf16(&tmA, x, 4, dims, str, box)) return 1;
+    uint64_t str[3] = {(uint64_t)Cin_p * esz, (uint64_t)W * Cin_p * esz, (uint64_t)H * W * Cin_p * esz};
+    uint32_t box[4] = {(uint32_t)a.CB, (uint32_t)BW, (uint32_t)(MS * BH + KH - 1), 1};
+    if (encode_tmap_act(&tmA, x, 4, dims, str, box, act, false)) return 1;
   }
   {
     const uint64_t Ktot = (uint64_t)KH * KW * Cin_p;
     uint64_t dims[2] = {Ktot, (uint64_t)Np16};
-    uint64_t str[1] = {Ktot * 2};
-    uint32_t box[2] = {64, (uint32_t)n_tile};
-    if (encode_tmap_bf16(&tmB, wpack, 2, dims, str, box)) return 1;
+    uint64_t str[1] = {Ktot * esz};
+    uint32_t box[2] = {(uint32_t)a.CB, (uint32_t)n_tile};
+    if (encode_tmap_act(&tmB, wpack, 2, dims, str, box, act, false)) return 1;
   }
   const size_t smem = (size_t)stages * a.stage_bytes + 1024 + (2 * stages + 1) * 8 + 16;
   static bool attr_set[64] = {false};
   int dev = 0;
   DTDL_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
-    DTDL_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_v2_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));  // 227 KB less the static epilogue accumulators
+    // 227 KB less the static epilogue accumulators
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_v2_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_v2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024));
     attr_set[dev & 63] = true;
   }
   dim3 grid(N * a.tiles_h, n_tiles);
-  conv_gemm_v2_kernel<<<grid, 256, smem, stream>>>(tmA, tmB, a);
+  if (act == kActF32)
+    conv_gemm_v2_kernel<1><<<grid, 256, smem, stream>>>(tmA, tmB, a);
+  else
+    conv_gemm_v2_kernel<0><<<grid, 256, smem, stream>>>(tmA, tmB, a);
   DTDL_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -18,6 +18,12 @@
 // result is bitwise reproducible, unlike an atomic split-K) and writes the
 // fp32 gradient in the OIHW layout of the torch parameter.
 //
+// Two instantiations (see conv_gemm.cu): ACT = 0 bf16 operands, boxes of 64 channels, 16 pixels per
+// MMA; ACT = 1 fp32 operands read as TF32, boxes of 32 channels (128 bytes), 8 pixels per MMA.
+// MN-major 32-bit operands must use tcgen05's SWIZZLE_128B_BASE32B layout (32-byte swizzle atoms,
+// 4-row groups), which the TMA produces with CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B.
+// A stride-2 convolution samples x through TMA element strides (row mode only).
+//
 // Capability covered: K-O4 / K-O12 of SURVEY.md section 2.5 (the reference
 // reaches cuDNN/cuBLAS through autograd of nn.Conv2d / nn.Linear:
 // pytorch/model.py:28-32,77; pytorch/single_gpu.py:102).
@@ -31,12 +37,17 @@ void choose_pixel_tile(int N, int Ho, int Wo, int* BW, int* BH, int* BNi);
 
 struct WgradArgs {
   int KW, pad_h, pad_w;
-  int groups_per_row;  // ceil(KW / 3)
+  int stride;          // 1 or 2 (2: row mode)
+  int CB;              // channels per box: 64 (bf16) / 32 (fp32)
+  int n_boxes;         // x boxes per filter column: 64 / CB
+  int cols_per_cta;    // row mode: filter columns per CTA (3 bf16, 1 fp32)
+  int x_box_bytes;     // bytes between the x boxes of one stage
+  int groups_per_row;  // ceil(KW / cols_per_cta)
   int BW, BH, BNi, rows, kslices;
   int tiles_w, tiles_h, tiles_n, n_ptiles;
   int tiles_per_split;
   int ci_chunks;
-  int m_boxes;  // 1 when Cout_p <= 64 (second dy box never loaded)
+  int m_boxes;  // dy boxes per stage: ceil(min(Cout_p, 128) / CB) (the others are never loaded)
   int Cout_p, Cin_w, taps;
   int stages, stage_bytes;
   int zero_fill;
@@ -47,6 +58,7 @@ struct WgradArgs {
 
 static constexpr int kBox = 128 * 128;  // [128 pixel rows][64 bf16]
 
+template <int ACT>
 __global__ void __launch_bounds__(256, 2)
 conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ CUtensorMap tmX,
                   const WgradArgs a) {
@@ -66,8 +78,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constan
   // col mode : CTA = filter column s0, all KH filter rows, ONE x halo box; the operand of filter
   //            row r is that box viewed r image rows (r*BW*128 bytes, 1 KB aligned) further down
   const int r = a.col_mode ? 0 : blockIdx.y / a.groups_per_row;
-  const int s0 = a.col_mode ? blockIdx.y : (blockIdx.y % a.groups_per_row) * 3;
-  const int ns = a.col_mode ? a.KH : ((a.KW - s0) < 3 ? (a.KW - s0) : 3);
+  const int s0 = a.col_mode ? blockIdx.y : (blockIdx.y % a.groups_per_row) * a.cols_per_cta;
+  const int ns = a.col_mode ? a.KH : ((a.KW - s0) < a.cols_per_cta ? (a.KW - s0) : a.cols_per_cta);
   const int co_tile = blockIdx.z / a.ci_chunks;
   const int ci_chunk = blockIdx.z % a.ci_chunks;
   const int co0 = co_tile * 128, ci0 = ci_chunk * 64;
@@ -108,8 +120,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constan
 
   if (warp == 0) {
     if (elect_one()) {
-      const uint32_t tx = a.col_mode ? (uint32_t)(a.rows * 128 * a.m_boxes + a.halo_rows * 128)
-                                     : (uint32_t)(a.rows * 128 * (a.m_boxes + ns));
+      const uint32_t tx = a.col_mode ? (uint32_t)(a.rows * 128 * a.m_boxes + a.halo_rows * 128 * a.n_boxes)
+                                     : (uint32_t)(a.rows * 128 * (a.m_boxes + ns * a.n_boxes));
       int stage = 0, phase = 0;
       for (int pt = pt_begin; pt < pt_end; ++pt) {
         int t = pt;
@@ -121,13 +133,16 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constan
         mbar_wait(&empty[stage], phase ^ 1, 11);
         mbar_arrive_expect_tx(&full[stage], tx);
         for (int b = 0; b < a.m_boxes; ++b)
-          tma_load_4d(st + b * kBox, &tmDy, &full[stage], co0 + b * 64, w0, h0, n0);
+          tma_load_4d(st + b * kBox, &tmDy, &full[stage], co0 + b * a.CB, w0, h0, n0);
         if (a.col_mode) {
-          tma_load_4d(st + a.x_off, &tmX, &full[stage], ci0, w0 + s0 - a.pad_w, h0 - a.pad_h, n0);
+          for (int nb = 0; nb < a.n_boxes; ++nb)
+            tma_load_4d(st + a.x_off + nb * a.x_box_bytes, &tmX, &full[stage], ci0 + nb * a.CB,
+                        w0 + s0 - a.pad_w, h0 - a.pad_h, n0);
         } else {
           for (int s = 0; s < ns; ++s)
-            tma_load_4d(st + (2 + s) * kBox, &tmX, &full[stage], ci0, w0 + s0 + s - a.pad_w,
-                        h0 + r - a.pad_h, n0);
+            for (int nb = 0; nb < a.n_boxes; ++nb)
+              tma_load_4d(st + a.x_off + (s * a.n_boxes + nb) * kBox, &tmX, &full[stage], ci0 + nb * a.CB,
+                          a.stride * w0 + s0 + s - a.pad_w, a.stride * h0 + r - a.pad_h, n0);
         }
         if (++stage == a.stages) {
           stage = 0;
@@ -137,29 +152,36 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constan
     }
   } else if (warp == 1) {
     if (elect_one()) {
-      const uint32_t idesc = umma_idesc_bf16(128, 64, 1, 1);
-      const uint64_t desc0 = umma_smem_desc(smem_u32(smem), kBox, 1024);
-      uint32_t koff[8];  // byte offset of K slice k inside the B operand (computed once)
+      constexpr int kPix = ACT ? 8 : 16;          // pixels (K) per MMA
+      constexpr uint32_t kSlice = kPix * 128;     // bytes of one K slice
+      constexpr int kMaxSlices = 128 / kPix;
+      const uint32_t idesc = umma_idesc<ACT>(128, 64, 1, 1);
+      // bf16: SWIZZLE_128B, 8-row K groups; fp32: SWIZZLE_128B_BASE32B, 4-row K groups
+      const uint32_t layout = ACT ? 1u : 2u, sbo = ACT ? 512u : 1024u;
+      const uint64_t adesc0 = umma_smem_desc(smem_u32(smem), kBox, sbo, layout);
+      const uint64_t bdesc0 = umma_smem_desc(smem_u32(smem), (uint32_t)a.x_box_bytes, sbo, layout);
+      uint32_t koff[kMaxSlices];  // byte offset of K slice k inside the B operand (computed once)
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const int kpi = (a.BW * a.BH) >> 4;
-        koff[k] = a.col_mode ? (uint32_t)(((k / kpi) * (a.BH + a.KH - 1) * a.BW) * 128 + (k % kpi) * 2048)
-                             : (uint32_t)(k * 2048);
+      for (int k = 0; k < kMaxSlices; ++k) {
+        const int kpi = (a.BW * a.BH) / kPix;
+        koff[k] = a.col_mode ? (uint32_t)(((k / kpi) * (a.BH + a.KH - 1) * a.BW) * 128 + (k % kpi) * kSlice)
+                             : (uint32_t)(k * kSlice);
       }
       int stage = 0, phase = 0;
       for (int i = 0; i < n_steps; ++i) {
         mbar_wait(&full[stage], phase, 12);
         tc_fence_after();
-        const uint64_t ad0 = umma_desc_advance(desc0, (uint32_t)(stage * a.stage_bytes));
+        const uint64_t ad0 = umma_desc_advance(adesc0, (uint32_t)(stage * a.stage_bytes));
+        const uint64_t bs0 = umma_desc_advance(bdesc0, (uint32_t)(stage * a.stage_bytes + a.x_off));
         for (int s = 0; s < ns; ++s) {
-          // B operand of accumulator s: row mode = its own shifted box; col mode = the halo box
+          // B operand of accumulator s: row mode = its own shifted box(es); col mode = the halo box
           // viewed s image rows further down (koff[] already holds the per-slice image jumps)
-          const uint64_t bd0 = umma_desc_advance(ad0, a.col_mode ? (uint32_t)(a.x_off + s * a.BW * 128)
-                                                                : (uint32_t)((2 + s) * kBox));
+          const uint64_t bd0 = umma_desc_advance(bs0, a.col_mode ? (uint32_t)(s * a.BW * 128)
+                                                                : (uint32_t)(s * a.n_boxes * kBox));
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
+          for (int k = 0; k < kMaxSlices; ++k) {
             if (k < a.kslices)
-              umma_bf16(tmem_base + s * 64, umma_desc_advance(ad0, k * 2048), umma_desc_advance(bd0, koff[k]),
+              umma<ACT>(tmem_base + s * 64, umma_desc_advance(ad0, k * kSlice), umma_desc_advance(bd0, koff[k]),
                         idesc, (i > 0 || k > 0) ? 1u : 0u);
           }
         }
@@ -267,34 +289,42 @@ wgrad_reduce_kernel(const float* __restrict__ ws, float* __restrict__ dw, int sp
 using namespace dtdl;
 
 #include <stdlib.h>
+#include <atomic>
 static int wgrad_waves() {
   static int w = getenv("DTDL_WGRAD_WAVES") ? atoi(getenv("DTDL_WGRAD_WAVES")) : 2;
   return w < 1 ? 1 : w;
 }
 
 // Plans the split-K decomposition; shared by the size query and the launch.
-static void wgrad_plan(int N, int Ho, int Wo, int Cin_p, int Cout_p, int KH, int KW, WgradArgs* a,
-                       int* splits) {
+static void wgrad_plan(int N, int Ho, int Wo, int Cin_p, int Cout_p, int KH, int KW, int stride, int act,
+                       WgradArgs* a, int* splits) {
+  const int kpix = act == kActF32 ? 8 : 16;
   choose_pixel_tile(N, Ho, Wo, &a->BW, &a->BH, &a->BNi);
   a->rows = a->BW * a->BH * a->BNi;
-  a->kslices = (a->rows + 15) / 16;
-  a->zero_fill = (a->rows % 16) != 0;
+  a->kslices = (a->rows + kpix - 1) / kpix;
+  a->zero_fill = (a->rows % kpix) != 0;
+  a->stride = stride;
+  a->CB = act == kActF32 ? 32 : 64;
+  a->n_boxes = 64 / a->CB;
+  a->cols_per_cta = act == kActF32 ? 1 : 3;
   a->tiles_w = (Wo + a->BW - 1) / a->BW;
   a->tiles_h = (Ho + a->BH - 1) / a->BH;
   a->tiles_n = (N + a->BNi - 1) / a->BNi;
   a->n_ptiles = a->tiles_w * a->tiles_h * a->tiles_n;
   a->KW = KW;
-  a->groups_per_row = (KW + 2) / 3;
+  a->groups_per_row = (KW + a->cols_per_cta - 1) / a->cols_per_cta;
   a->ci_chunks = (Cin_p + 63) / 64;
   a->Cin_w = a->ci_chunks * 64;
   a->Cout_p = Cout_p;
-  a->m_boxes = Cout_p <= 64 ? 1 : 2;
+  a->m_boxes = ((Cout_p < 128 ? Cout_p : 128) + a->CB - 1) / a->CB;
   a->taps = KH * KW;
   a->KH = KH;
   static const bool no_col = getenv("DTDL_WGRAD_ROWMODE") != nullptr;
-  a->col_mode = (!no_col && a->BW % 8 == 0 && (a->BW * a->BH) % 16 == 0 && a->rows == 128 && KH <= 4 && KH > 1) ? 1 : 0;
+  a->col_mode = (!no_col && stride == 1 && a->BW % 8 == 0 && (a->BW * a->BH) % 16 == 0 && a->rows == 128 &&
+                 KH <= 4 && KH > 1) ? 1 : 0;
   a->halo_rows = a->BNi * (a->BH + KH - 1) * a->BW;
   a->x_off = a->m_boxes * kBox;
+  a->x_box_bytes = a->col_mode ? (a->halo_rows * 128 + 1023) / 1024 * 1024 : kBox;
   const int co_tiles = (Cout_p + 127) / 128;
   const int groups = (a->col_mode ? KW : KH * a->groups_per_row) * co_tiles * a->ci_chunks;
   // few output tiles (narrow layers): one wave of fat CTAs amortises set-up and halves the
@@ -308,67 +338,90 @@ static void wgrad_plan(int N, int Ho, int Wo, int Cin_p, int Cout_p, int KH, int
   *splits = sp;
 }
 
-extern "C" long long dtdl_conv_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cin_p, int Cout_p,
-                                                     int KH, int KW) {
+// The scratch need depends on the split count only, which does not depend on stride or act for a
+// given OUTPUT size -- except through the operating mode (stride 2 and fp32 use more CTA groups).
+// Callers size for the mode they run; this entry point keeps the bf16 stride-1 figure and
+// dtdl_conv_wgrad_workspace_bytes_ex answers for any mode.
+extern "C" long long dtdl_conv_wgrad_workspace_bytes_ex(int N, int Ho, int Wo, int Cin_p, int Cout_p,
+                                                        int KH, int KW, int stride, int act) {
   WgradArgs a;
   int splits;
-  wgrad_plan(N, Ho, Wo, Cin_p, Cout_p, KH, KW, &a, &splits);
+  wgrad_plan(N, Ho, Wo, Cin_p, Cout_p, KH, KW, stride, act, &a, &splits);
   return (long long)splits * a.taps * Cout_p * a.Cin_w * 4;
 }
 
-extern "C" int dtdl_conv_wgrad(const void* x, const void* dy, float* dw, void* workspace,
-                               long long workspace_bytes, int N, int H, int W, int Cin, int Cin_p,
-                               int Ho, int Wo, int Cout, int Cout_p, int KH, int KW, int pad_h,
-                               int pad_w, int accumulate, void* stream_) {
+extern "C" long long dtdl_conv_wgrad_workspace_bytes(int N, int Ho, int Wo, int Cin_p, int Cout_p,
+                                                     int KH, int KW) {
+  return dtdl_conv_wgrad_workspace_bytes_ex(N, Ho, Wo, Cin_p, Cout_p, KH, KW, 1, kActBf16);
+}
+
+static int conv_wgrad_impl(const void* x, const void* dy, float* dw, void* workspace,
+                           long long workspace_bytes, int N, int H, int W, int Cin, int Cin_p, int Ho,
+                           int Wo, int Cout, int Cout_p, int KH, int KW, int pad_h, int pad_w,
+                           int accumulate, int stride, int act, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  DTDL_REQUIRE(act == kActBf16 || act == kActF32, "act must be 0 (bf16) or 1 (fp32 / TF32)");
   DTDL_REQUIRE(Cin_p % 8 == 0 && Cout_p % 8 == 0, "channel counts must be padded to 8");
-  DTDL_REQUIRE(Ho >= 1 && Wo >= 1 && Ho <= H + 2 * pad_h - KH + 1 && Wo <= W + 2 * pad_w - KW + 1,
-               "output size does not match a stride-1 convolution");
+  DTDL_REQUIRE(stride == 1 || stride == 2, "stride 1 or 2");
+  DTDL_REQUIRE(Ho >= 1 && Wo >= 1 && Ho <= (H + 2 * pad_h - KH) / stride + 1 &&
+                   Wo <= (W + 2 * pad_w - KW) / stride + 1,
+               "output size does not match the convolution");
+  const int esz = act_esize(act);
   WgradArgs a;
   int splits;
-  wgrad_plan(N, Ho, Wo, Cin_p, Cout_p, KH, KW, &a, &splits);
+  wgrad_plan(N, Ho, Wo, Cin_p, Cout_p, KH, KW, stride, act, &a, &splits);
   a.pad_h = pad_h;
   a.pad_w = pad_w;
   const long long need = (long long)splits * a.taps * Cout_p * a.Cin_w * 4;
   DTDL_REQUIRE(workspace != nullptr && workspace_bytes >= need,
-               "wgrad workspace too small (see dtdl_conv_wgrad_workspace_bytes)");
+               "wgrad workspace too small (see dtdl_conv_wgrad_workspace_bytes_ex)");
   a.ws = reinterpret_cast<float*>(workspace);
   if (a.col_mode) {
-    a.stage_bytes = a.x_off + (a.halo_rows * 128 + 1023) / 1024 * 1024;  // dy box(es) + x halo box
+    a.stage_bytes = a.x_off + a.n_boxes * a.x_box_bytes;  // dy box(es) + x halo box(es)
     a.stages = a.stage_bytes <= 40 * 1024 ? 3 : 2;
   } else {
-    a.stage_bytes = 5 * kBox;  // 2 dy boxes + 3 shifted x boxes
+    // dy boxes + the shifted x boxes of this CTA's filter columns (bf16: <= 2 + 3, fp32: <= 4 + 2)
+    a.stage_bytes = a.x_off + a.cols_per_cta * a.n_boxes * kBox;
     a.stages = 2;
   }
+  // The MMA always reads M = 128 output channels = 128 / CB box slots from the start of a stage, loaded
+  // or not (rows of boxes that were not loaded are never stored): the slots must exist.
+  if (a.stage_bytes < (128 / a.CB) * kBox) a.stage_bytes = (128 / a.CB) * kBox;
   const int steps = a.tiles_per_split;
   if (steps < a.stages) a.stages = steps < 1 ? 1 : steps;
 
   CUtensorMap tmDy, tmX;
   {
     uint64_t dims[4] = {(uint64_t)Cout_p, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)N};
-    uint64_t str[3] = {(uint64_t)Cout_p * 2, (uint64_t)Wo * Cout_p * 2,
-                       (uint64_t)Ho * Wo * Cout_p * 2};
-    uint32_t box[4] = {64, (uint32_t)a.BW, (uint32_t)a.BH, (uint32_t)a.BNi};
-    if (encode_tmap_bf16(&tmDy, dy, 4, dims, str, box)) return 1;
+    uint64_t str[3] = {(uint64_t)Cout_p * esz, (uint64_t)Wo * Cout_p * esz,
+                       (uint64_t)Ho * Wo * Cout_p * esz};
+    uint32_t box[4] = {(uint32_t)a.CB, (uint32_t)a.BW, (uint32_t)a.BH, (uint32_t)a.BNi};
+    if (encode_tmap_act(&tmDy, dy, 4, dims, str, box, act, true)) return 1;
   }
   {
     uint64_t dims[4] = {(uint64_t)Cin_p, (uint64_t)W, (uint64_t)H, (uint64_t)N};
-    uint64_t str[3] = {(uint64_t)Cin_p * 2, (uint64_t)W * Cin_p * 2, (uint64_t)H * W * Cin_p * 2};
-    uint32_t box[4] = {64, (uint32_t)a.BW, (uint32_t)(a.col_mode ? a.BH + KH - 1 : a.BH), (uint32_t)a.BNi};
-    if (encode_tmap_bf16(&tmX, x, 4, dims, str, box)) return 1;
+    uint64_t str[3] = {(uint64_t)Cin_p * esz, (uint64_t)W * Cin_p * esz, (uint64_t)H * W * Cin_p * esz};
+    uint32_t box[4] = {(uint32_t)a.CB, (uint32_t)(a.BW * stride),
+                       (uint32_t)((a.col_mode ? a.BH + KH - 1 : a.BH) * stride), (uint32_t)a.BNi};
+    uint32_t est[4] = {1, (uint32_t)stride, (uint32_t)stride, 1};
+    if (encode_tmap_act(&tmX, x, 4, dims, str, box, act, true, est)) return 1;
   }
   const size_t smem = (size_t)a.stages * a.stage_bytes + 1024 + (2 * a.stages + 1) * 8 + 16;
+  DTDL_REQUIRE(smem <= 227 * 1024, "wgrad pipeline does not fit in shared memory");
   static bool attr_set[64] = {false};
   int dev = 0;
   DTDL_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr_set[dev & 63]) {
-    DTDL_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr_set[dev & 63] = true;
   }
   const int co_tiles = (Cout_p + 127) / 128;
   dim3 grid(splits, a.col_mode ? KW : KH * a.groups_per_row, co_tiles * a.ci_chunks);
-  conv_wgrad_kernel<<<grid, 256, smem, stream>>>(tmDy, tmX, a);
+  if (act == kActF32)
+    conv_wgrad_kernel<1><<<grid, 256, smem, stream>>>(tmDy, tmX, a);
+  else
+    conv_wgrad_kernel<0><<<grid, 256, smem, stream>>>(tmDy, tmX, a);
   DTDL_CHECK_CUDA(cudaGetLastError());
 
   dim3 rgrid((a.taps * (a.Cin_w / 4) + 63) / 64, Cout);
@@ -376,6 +429,14 @@ extern "C" int dtdl_conv_wgrad(const void* x, const void* dy, float* dw, void* w
                                                  a.Cin_w, accumulate);
   DTDL_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+extern "C" int dtdl_conv_wgrad(const void* x, const void* dy, float* dw, void* workspace,
+                               long long workspace_bytes, int N, int H, int W, int Cin, int Cin_p,
+                               int Ho, int Wo, int Cout, int Cout_p, int KH, int KW, int pad_h,
+                               int pad_w, int accumulate, int stride, int act, void* stream_) {
+  return conv_wgrad_impl(x, dy, dw, workspace, workspace_bytes, N, H, W, Cin, Cin_p, Ho, Wo, Cout, Cout_p,
+                         KH, KW, pad_h, pad_w, accumulate, stride, act, stream_);
 }
 
 // ---------------------------------------------------------------------------
@@ -417,16 +478,18 @@ extern "C" int dtdl_conv_wgrad_static(const void* x, const void* dy, float* dw, 
                                       int Cin, int Cin_p, int Ho, int Wo, int Cout, int Cout_p,
                                       int KH, int KW, int pad_h, int pad_w, int accumulate,
                                       void* stream_) {
-  static void* scratch_of_device[64] = {nullptr};
+  // one slot per device; atomic because host threads driving different streams may race here
+  // (both would store the same address, so a plain exchange is enough)
+  static std::atomic<void*> scratch_of_device[64];
   int dev = 0;
   DTDL_CHECK_CUDA(cudaGetDevice(&dev));
   DTDL_REQUIRE(dev >= 0 && dev < 64, "device index out of range for the static scratch table");
-  if (scratch_of_device[dev] == nullptr) {
+  void* scratch = scratch_of_device[dev].load(std::memory_order_acquire);
+  if (scratch == nullptr) {
     // first call on this device: resolve the device address of the array
-    void* p = nullptr;
-    DTDL_CHECK_CUDA(cudaGetSymbolAddress(&p, g_wgrad_static_scratch));
-    DTDL_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null scratch address");
-    scratch_of_device[dev] = p;
+    DTDL_CHECK_CUDA(cudaGetSymbolAddress(&scratch, g_wgrad_static_scratch));
+    DTDL_REQUIRE(scratch != nullptr, "cudaGetSymbolAddress returned a null scratch address");
+    scratch_of_device[dev].store(scratch, std::memory_order_release);
   }
   const long long need = dtdl_conv_wgrad_workspace_bytes(N, Ho, Wo, Cin_p, Cout_p, KH, KW);
   if (need > kStaticScratchBytes) {
@@ -436,6 +499,6 @@ extern "C" int dtdl_conv_wgrad_static(const void* x, const void* dy, float* dw, 
                    "; use dtdl_conv_wgrad with a caller-provided workspace");
     return 3;
   }
-  return dtdl_conv_wgrad(x, dy, dw, scratch_of_device[dev], kStaticScratchBytes, N, H, W, Cin, Cin_p,
-                         Ho, Wo, Cout, Cout_p, KH, KW, pad_h, pad_w, accumulate, stream_);
+  return conv_wgrad_impl(x, dy, dw, scratch, kStaticScratchBytes, N, H, W, Cin, Cin_p,
+                         Ho, Wo, Cout, Cout_p, KH, KW, pad_h, pad_w, accumulate, 1, kActBf16, stream_);
 }

@@ -32,19 +32,47 @@ __device__ __forceinline__ float warp_reduce_scatter32(float (&v)[32], int lane)
 }
 
 // One 16-column chunk of one warp's 32 rows -> this warp's row of partial sums.  `first` is false
-// when the warp visits the same columns again (second sub-tile of the halo kernel).
+// when the warp visits the same columns again (second sub-tile of the halo kernel).  ROUND_BF16:
+// the statistics are those of the stored bf16 values (fp32 outputs are summed as they are).
+template <bool ROUND_BF16>
 __device__ __forceinline__ void epilogue_col_stats_part(const float (&f)[16], bool valid, int lane,
                                                         float* part, int n_tile, int jcol, bool first) {
   float v[32];
 #pragma unroll
   for (int i = 0; i < 16; ++i) {
-    const float x = valid ? __bfloat162float(__float2bfloat16(f[i])) : 0.f;
+    const float x = !valid ? 0.f : (ROUND_BF16 ? __bfloat162float(__float2bfloat16(f[i])) : f[i]);
     v[i] = x;
     v[16 + i] = x * x;
   }
   const float tot = warp_reduce_scatter32(v, lane);
   float* dst = part + (lane < 16 ? 0 : n_tile) + jcol + (lane & 15);
   *dst = first ? tot : *dst + tot;
+}
+
+// 16 consecutive output channels of one pixel; `remain` = channels left in the row from f[0] on
+// (a multiple of 8: rows are padded to 8 channels, tiles to 16).
+__device__ __forceinline__ void epilogue_store_f32(float* out, const float (&f)[16], int remain) {
+#pragma unroll
+  for (int h = 0; h < 4; ++h)
+    if (h * 4 < remain)
+      *reinterpret_cast<float4*>(out + h * 4) = make_float4(f[h * 4], f[h * 4 + 1], f[h * 4 + 2], f[h * 4 + 3]);
+}
+__device__ __forceinline__ void epilogue_store_bf16(__nv_bfloat16* out, const float (&f)[16], int remain) {
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    if (h * 8 < remain) {
+      uint4 pk;
+      __nv_bfloat162 p0 = __floats2bfloat162_rn(f[h * 8 + 0], f[h * 8 + 1]);
+      __nv_bfloat162 p1 = __floats2bfloat162_rn(f[h * 8 + 2], f[h * 8 + 3]);
+      __nv_bfloat162 p2 = __floats2bfloat162_rn(f[h * 8 + 4], f[h * 8 + 5]);
+      __nv_bfloat162 p3 = __floats2bfloat162_rn(f[h * 8 + 6], f[h * 8 + 7]);
+      pk.x = *reinterpret_cast<uint32_t*>(&p0);
+      pk.y = *reinterpret_cast<uint32_t*>(&p1);
+      pk.z = *reinterpret_cast<uint32_t*>(&p2);
+      pk.w = *reinterpret_cast<uint32_t*>(&p3);
+      *reinterpret_cast<uint4*>(out + h * 8) = pk;
+    }
+  }
 }
 
 // named barrier over the 128 epilogue threads (id 1; id 0 is __syncthreads)

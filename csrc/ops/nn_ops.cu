@@ -1,6 +1,9 @@
-// Bandwidth-bound layer kernels on NHWC bf16 activations whose channel count is
-// padded to a multiple of 8 (one 16-byte vector = 8 channels of one pixel).
-// Pad channels are kept at exactly zero by every kernel here.
+// Bandwidth-bound layer kernels on NHWC activations whose channel count is padded
+// to a multiple of 8.  Pad channels are kept at exactly zero by every kernel here.
+// Every kernel is instantiated for both activation storage types: a thread always
+// moves one 16-byte vector, i.e. V = 8 channels of bf16 (act 0) or V = 4 channels
+// of fp32 (act 1, the reference's own precision: pytorch/single_gpu.py:65-66 keeps
+// the model in fp32).  Arithmetic and statistics are fp32 in both.
 //
 //   batch norm (train/eval) forward  : stats reduction + fused apply(+residual)(+ReLU)
 //   batch norm backward              : fused (ReLU mask) reduction + apply
@@ -17,25 +20,41 @@
 
 namespace dtdl {
 
-struct F8 {
-  float v[8];
+// V channels of one pixel as floats; V = 8 <-> a uint4 of bf16, V = 4 <-> a uint4 of fp32.
+template <int V>
+struct FV {
+  float v[V];
 };
-__device__ __forceinline__ F8 unpack8(uint4 u) {
-  F8 r;
-  const __nv_bfloat162* p = reinterpret_cast<const __nv_bfloat162*>(&u);
+template <int V>
+__device__ __forceinline__ FV<V> unpackv(uint4 u) {
+  FV<V> r;
+  if (V == 8) {
+    const __nv_bfloat162* p = reinterpret_cast<const __nv_bfloat162*>(&u);
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    float2 f = __bfloat1622float2(p[i]);
-    r.v[2 * i] = f.x;
-    r.v[2 * i + 1] = f.y;
+    for (int i = 0; i < V / 2; ++i) {
+      float2 f = __bfloat1622float2(p[i]);
+      r.v[2 * i] = f.x;
+      r.v[2 * i + 1] = f.y;
+    }
+  } else {
+    r.v[0] = __uint_as_float(u.x);
+    r.v[1] = __uint_as_float(u.y);
+    r.v[2] = __uint_as_float(u.z);
+    r.v[3] = __uint_as_float(u.w);
   }
   return r;
 }
-__device__ __forceinline__ uint4 pack8(const F8& f) {
+template <int V>
+__device__ __forceinline__ uint4 packv(const FV<V>& f) {
   uint4 u;
-  __nv_bfloat162* p = reinterpret_cast<__nv_bfloat162*>(&u);
+  if (V == 8) {
+    __nv_bfloat162* p = reinterpret_cast<__nv_bfloat162*>(&u);
 #pragma unroll
-  for (int i = 0; i < 4; ++i) p[i] = __floats2bfloat162_rn(f.v[2 * i], f.v[2 * i + 1]);
+    for (int i = 0; i < V / 2; ++i) p[i] = __floats2bfloat162_rn(f.v[2 * i], f.v[2 * i + 1]);
+  } else {
+    u = make_uint4(__float_as_uint(f.v[0]), __float_as_uint(f.v[1]), __float_as_uint(f.v[2]),
+                   __float_as_uint(f.v[3]));
+  }
   return u;
 }
 
@@ -54,6 +73,7 @@ static inline int grid_for(long long work_items, int per_block, int max_blocks) 
 // ---------------------------------------------------------------------------
 // NCHW fp32 -> NHWC bf16 (channel padded).  One thread per (pixel, 8-channel group).
 // ---------------------------------------------------------------------------
+template <int V>
 __global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, uint4* __restrict__ y, int N, int C,
                                     int HW, int G) {
   const long long total = (long long)N * HW * G;
@@ -63,19 +83,20 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ x, uint4* __restri
     const long long pix = i / G;
     const int hw = (int)(pix % HW);
     const long long n = pix / HW;
-    F8 f;
+    FV<V> f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int c = g * 8 + k;
+    for (int k = 0; k < V; ++k) {
+      const int c = g * V + k;
       f.v[k] = c < C ? x[(n * C + c) * HW + hw] : 0.f;
     }
-    y[i] = pack8(f);
+    y[i] = packv<V>(f);
   }
 }
 
 // NCHW fp32 -> 2x2 space-to-depth NHWC bf16: y[n, ho, wo, (bh*2+bw)*C + c] = x[n, c, 2ho+bh, 2wo+bw].
 // Turns a stride-2 KxK convolution into a stride-1 ceil(K/2) x ceil(K/2) one over 4C channels
 // (ResNet's 7x7/2 stem becomes 4x4/1 over 12 channels).
+template <int V>
 __global__ void nchw_to_s2d_kernel(const float* __restrict__ x, uint4* __restrict__ y, int N, int C,
                                    int H, int W, int G) {
   const int Ho = H / 2, Wo = W / 2;
@@ -88,10 +109,10 @@ __global__ void nchw_to_s2d_kernel(const float* __restrict__ x, uint4* __restric
     t /= Wo;
     const int ho = (int)(t % Ho);
     const long long n = t / Ho;
-    F8 f;
+    FV<V> f;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int ch = g * 8 + k;
+    for (int k = 0; k < V; ++k) {
+      const int ch = g * V + k;
       float v = 0.f;
       if (ch < 4 * C) {
         const int phase = ch / C, c = ch % C;
@@ -99,46 +120,47 @@ __global__ void nchw_to_s2d_kernel(const float* __restrict__ x, uint4* __restric
       }
       f.v[k] = v;
     }
-    y[i] = pack8(f);
+    y[i] = packv<V>(f);
   }
 }
 
 // ---------------------------------------------------------------------------
 // Per-channel sum / sum of squares (accumulated with atomics into sums[2*Cp]).
 // ---------------------------------------------------------------------------
+template <int V>
 __global__ void bn_stats_kernel(const uint4* __restrict__ x, float* __restrict__ sums, long long P,
                                 int G) {
   extern __shared__ float red[];  // [rows][G][16]
   const int rows = blockDim.x / G;
   const int g = threadIdx.x % G, rrow = threadIdx.x / G;
-  float s1[8], s2[8];
+  float s1[V], s2[V];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) s1[k] = s2[k] = 0.f;
+  for (int k = 0; k < V; ++k) s1[k] = s2[k] = 0.f;
   for (long long p = (long long)blockIdx.x * rows + rrow; p < P; p += (long long)gridDim.x * rows) {
-    const F8 f = unpack8(x[p * G + g]);
+    const FV<V> f = unpackv<V>(x[p * G + g]);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
+    for (int k = 0; k < V; ++k) {
       s1[k] += f.v[k];
       s2[k] += f.v[k] * f.v[k];
     }
   }
-  float* mine = red + (size_t)threadIdx.x * 16;
+  float* mine = red + (size_t)threadIdx.x * (2 * V);
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
+  for (int k = 0; k < V; ++k) {
     mine[k] = s1[k];
-    mine[8 + k] = s2[k];
+    mine[V + k] = s2[k];
   }
   __syncthreads();
   // threads [0, G*16) each own one (g, k) pair and sum it over the rows
-  for (int o = threadIdx.x; o < G * 16; o += blockDim.x) {
-    const int og = o / 16, ok = o % 16;
+  for (int o = threadIdx.x; o < G * 2 * V; o += blockDim.x) {
+    const int og = o / (2 * V), ok = o % (2 * V);
     float acc = 0.f;
-    for (int rr = 0; rr < rows; ++rr) acc += red[((size_t)rr * G + og) * 16 + ok];
-    const int Cp = G * 8;
-    if (ok < 8)
-      atomicAdd(&sums[og * 8 + ok], acc);
+    for (int rr = 0; rr < rows; ++rr) acc += red[((size_t)rr * G + og) * (2 * V) + ok];
+    const int Cp = G * V;
+    if (ok < V)
+      atomicAdd(&sums[og * V + ok], acc);
     else
-      atomicAdd(&sums[Cp + og * 8 + (ok - 8)], acc);
+      atomicAdd(&sums[Cp + og * V + (ok - V)], acc);
   }
 }
 
@@ -171,8 +193,9 @@ struct BnApplyArgs {
 
 // Per-channel scale/shift into shared memory; block 0 also writes the saved / running statistics
 // and resets `zero_buf`.  Ends with __syncthreads().
+template <int V>
 __device__ __forceinline__ void bn_apply_prologue(const BnApplyArgs& a, float* sc, float* sh) {
-  const int Cp = a.G * 8;
+  const int Cp = a.G * V;
   for (int c = threadIdx.x; c < Cp; c += blockDim.x) {
     float scale = 0.f, shift = 0.f;
     if (c < a.C) {
@@ -207,12 +230,13 @@ __device__ __forceinline__ void bn_apply_prologue(const BnApplyArgs& a, float* s
   __syncthreads();
 }
 
+template <int V>
 __global__ void bn_apply_kernel(const BnApplyArgs a) {
   extern __shared__ float ss[];  // scale[Cp], shift[Cp]
-  const int Cp = a.G * 8;
+  const int Cp = a.G * V;
   float* sc = ss;
   float* sh = ss + Cp;
-  bn_apply_prologue(a, sc, sh);
+  bn_apply_prologue<V>(a, sc, sh);
 
   const long long total = a.P * a.G;
   // (g, p) = (i % G, i / G) follow i by carry arithmetic: a 64-bit division per element is a
@@ -228,87 +252,89 @@ __global__ void bn_apply_kernel(const BnApplyArgs a) {
       g -= a.G;
       ++p;
     }
-    F8 f = unpack8(a.x[i]);
+    FV<V> f = unpackv<V>(a.x[i]);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) f.v[k] = f.v[k] * sc[g * 8 + k] + sh[g * 8 + k];
+    for (int k = 0; k < V; ++k) f.v[k] = f.v[k] * sc[g * V + k] + sh[g * V + k];
     if (a.residual != nullptr && g < a.Gres) {
-      const F8 r = unpack8(a.residual[p * a.Gres + g]);
+      const FV<V> r = unpackv<V>(a.residual[p * a.Gres + g]);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) f.v[k] += r.v[k];
+      for (int k = 0; k < V; ++k) f.v[k] += r.v[k];
     }
     if (a.relu) {
 #pragma unroll
-      for (int k = 0; k < 8; ++k) f.v[k] = fmaxf(f.v[k], 0.f);
+      for (int k = 0; k < V; ++k) f.v[k] = fmaxf(f.v[k], 0.f);
     }
-    a.y[i] = pack8(f);
+    a.y[i] = packv<V>(f);
   }
 }
 
 // Same, with the thread layout of bn_stats_kernel (a thread keeps its 8-channel group), so the
 // sums of the values it stores can ride along: the next BatchNorm needs no statistics pass.
+template <int V>
 __global__ void bn_apply_stats_kernel(const BnApplyArgs a) {
   extern __shared__ float ss[];  // scale[Cp], shift[Cp], red[blockDim][16]
-  const int Cp = a.G * 8;
+  const int Cp = a.G * V;
   float* sc = ss;
   float* sh = ss + Cp;
   float* red = ss + 2 * Cp;
-  bn_apply_prologue(a, sc, sh);
+  bn_apply_prologue<V>(a, sc, sh);
 
   const int G = a.G;
   const int rows = blockDim.x / G;
   const int g = threadIdx.x % G, rrow = threadIdx.x / G;
-  float s1[8], s2[8], kscale[8], kshift[8];
+  float s1[V], s2[V], kscale[V], kshift[V];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
+  for (int k = 0; k < V; ++k) {
     s1[k] = s2[k] = 0.f;
-    kscale[k] = sc[g * 8 + k];
-    kshift[k] = sh[g * 8 + k];
+    kscale[k] = sc[g * V + k];
+    kshift[k] = sh[g * V + k];
   }
   if (rrow < rows) {
     for (long long p = (long long)blockIdx.x * rows + rrow; p < a.P; p += (long long)gridDim.x * rows) {
-      F8 f = unpack8(a.x[p * G + g]);
+      FV<V> f = unpackv<V>(a.x[p * G + g]);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) f.v[k] = f.v[k] * kscale[k] + kshift[k];
+      for (int k = 0; k < V; ++k) f.v[k] = f.v[k] * kscale[k] + kshift[k];
       if (a.residual != nullptr && g < a.Gres) {
-        const F8 r = unpack8(a.residual[p * a.Gres + g]);
+        const FV<V> r = unpackv<V>(a.residual[p * a.Gres + g]);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) f.v[k] += r.v[k];
+        for (int k = 0; k < V; ++k) f.v[k] += r.v[k];
       }
       if (a.relu) {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) f.v[k] = fmaxf(f.v[k], 0.f);
+        for (int k = 0; k < V; ++k) f.v[k] = fmaxf(f.v[k], 0.f);
       }
-      const uint4 packed = pack8(f);
+      const uint4 packed = packv<V>(f);
       a.y[p * G + g] = packed;
-      const F8 q = unpack8(packed);  // statistics of what the consumer will read (bf16-rounded)
+      const FV<V> q = unpackv<V>(packed);  // statistics of what the consumer will read (bf16-rounded)
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
+      for (int k = 0; k < V; ++k) {
         s1[k] += q.v[k];
         s2[k] += q.v[k] * q.v[k];
       }
     }
   }
-  float* mine = red + (size_t)threadIdx.x * 16;
+  float* mine = red + (size_t)threadIdx.x * (2 * V);
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
+  for (int k = 0; k < V; ++k) {
     mine[k] = s1[k];
-    mine[8 + k] = s2[k];
+    mine[V + k] = s2[k];
   }
   __syncthreads();
-  for (int o = threadIdx.x; o < G * 16; o += blockDim.x) {
-    const int og = o / 16, ok = o % 16;
+  for (int o = threadIdx.x; o < G * 2 * V; o += blockDim.x) {
+    const int og = o / (2 * V), ok = o % (2 * V);
     float acc = 0.f;
-    for (int rr = 0; rr < rows; ++rr) acc += red[((size_t)rr * G + og) * 16 + ok];
-    if (ok < 8)
-      atomicAdd(&a.out_sums[og * 8 + ok], acc);
+    for (int rr = 0; rr < rows; ++rr) acc += red[((size_t)rr * G + og) * (2 * V) + ok];
+    if (ok < V)
+      atomicAdd(&a.out_sums[og * V + ok], acc);
     else
-      atomicAdd(&a.out_sums[Cp + og * 8 + (ok - 8)], acc);
+      atomicAdd(&a.out_sums[Cp + og * V + (ok - V)], acc);
   }
 }
 
 // ---------------------------------------------------------------------------
 // BN backward, pass 1: sums2[c] = sum g, sums2[Cp+c] = sum g * xhat, g = dy*[y>0]
 // ---------------------------------------------------------------------------
+template <int V>
 __global__ void bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x,
                                      const uint4* __restrict__ y, const float* __restrict__ mean,
                                      const float* __restrict__ rstd, float* __restrict__ sums2,
@@ -316,45 +342,45 @@ __global__ void bn_bwd_reduce_kernel(const uint4* __restrict__ dy, const uint4* 
   extern __shared__ float red[];
   const int rows = blockDim.x / G;
   const int g = threadIdx.x % G, rrow = threadIdx.x / G;
-  float m[8], rs[8], s1[8], s2[8];
+  float m[V], rs[V], s1[V], s2[V];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const int c = g * 8 + k;
+  for (int k = 0; k < V; ++k) {
+    const int c = g * V + k;
     m[k] = c < C ? mean[c] : 0.f;
     rs[k] = c < C ? rstd[c] : 0.f;
     s1[k] = s2[k] = 0.f;
   }
   for (long long p = (long long)blockIdx.x * rows + rrow; p < P; p += (long long)gridDim.x * rows) {
-    F8 d = unpack8(dy[p * G + g]);
-    const F8 xv = unpack8(x[p * G + g]);
+    FV<V> d = unpackv<V>(dy[p * G + g]);
+    const FV<V> xv = unpackv<V>(x[p * G + g]);
     if (relu) {
-      const F8 yv = unpack8(y[p * G + g]);
+      const FV<V> yv = unpackv<V>(y[p * G + g]);
 #pragma unroll
-      for (int k = 0; k < 8; ++k)
+      for (int k = 0; k < V; ++k)
         if (!(yv.v[k] > 0.f)) d.v[k] = 0.f;
     }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
+    for (int k = 0; k < V; ++k) {
       s1[k] += d.v[k];
       s2[k] += d.v[k] * (xv.v[k] - m[k]) * rs[k];
     }
   }
-  float* mine = red + (size_t)threadIdx.x * 16;
+  float* mine = red + (size_t)threadIdx.x * (2 * V);
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
+  for (int k = 0; k < V; ++k) {
     mine[k] = s1[k];
-    mine[8 + k] = s2[k];
+    mine[V + k] = s2[k];
   }
   __syncthreads();
-  for (int o = threadIdx.x; o < G * 16; o += blockDim.x) {
-    const int og = o / 16, ok = o % 16;
+  for (int o = threadIdx.x; o < G * 2 * V; o += blockDim.x) {
+    const int og = o / (2 * V), ok = o % (2 * V);
     float acc = 0.f;
-    for (int rr = 0; rr < rows; ++rr) acc += red[((size_t)rr * G + og) * 16 + ok];
-    const int Cp = G * 8;
-    if (ok < 8)
-      atomicAdd(&sums2[og * 8 + ok], acc);
+    for (int rr = 0; rr < rows; ++rr) acc += red[((size_t)rr * G + og) * (2 * V) + ok];
+    const int Cp = G * V;
+    if (ok < V)
+      atomicAdd(&sums2[og * V + ok], acc);
     else
-      atomicAdd(&sums2[Cp + og * 8 + (ok - 8)], acc);
+      atomicAdd(&sums2[Cp + og * V + (ok - V)], acc);
   }
 }
 
@@ -384,9 +410,10 @@ struct BnBwdArgs {
   const uint4* add_in;  // optional [P][Cp]: another gradient of the same input, summed into dx
 };
 
+template <int V>
 __global__ void bn_bwd_apply_kernel(const BnBwdArgs a) {
   extern __shared__ float ss[];  // k1[Cp] = gamma*rstd, k2[Cp] = mean_g, k3[Cp] = mean_gx*rstd, m, rs
-  const int Cp = a.G * 8;
+  const int Cp = a.G * V;
   float* k1 = ss;
   float* k2 = ss + Cp;
   float* k3 = ss + 2 * Cp;
@@ -428,61 +455,64 @@ __global__ void bn_bwd_apply_kernel(const BnBwdArgs a) {
       g -= a.G;
       ++p;
     }
-    F8 d = unpack8(a.dy[i]);
-    const F8 xv = unpack8(a.x[i]);
+    FV<V> d = unpackv<V>(a.dy[i]);
+    const FV<V> xv = unpackv<V>(a.x[i]);
     if (a.relu) {
-      const F8 yv = unpack8(a.y[i]);
+      const FV<V> yv = unpackv<V>(a.y[i]);
 #pragma unroll
-      for (int k = 0; k < 8; ++k)
+      for (int k = 0; k < V; ++k)
         if (!(yv.v[k] > 0.f)) d.v[k] = 0.f;
     }
-    if (a.dres != nullptr && g < a.Gres) a.dres[p * a.Gres + g] = pack8(d);
-    F8 o;
+    if (a.dres != nullptr && g < a.Gres) a.dres[p * a.Gres + g] = packv<V>(d);
+    FV<V> o;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int c = g * 8 + k;
+    for (int k = 0; k < V; ++k) {
+      const int c = g * V + k;
       const float xhat = (xv.v[k] - mm[c]) * rr[c];
       o.v[k] = k1[c] * (d.v[k] - k2[c] - xhat * k3[c]);
     }
     if (a.add_in != nullptr) {
-      const F8 e = unpack8(a.add_in[i]);
+      const FV<V> e = unpackv<V>(a.add_in[i]);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) o.v[k] += e.v[k];
+      for (int k = 0; k < V; ++k) o.v[k] += e.v[k];
     }
-    a.dx[i] = pack8(o);
+    a.dx[i] = packv<V>(o);
   }
 }
 
 // ---------------------------------------------------------------------------
 // relu backward on a saved output: dx = dy * [y > 0]
 // ---------------------------------------------------------------------------
+template <int V>
 __global__ void relu_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
                                 uint4* __restrict__ dx, long long n16) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16;
        i += (long long)gridDim.x * blockDim.x) {
-    F8 d = unpack8(dy[i]);
-    const F8 yv = unpack8(y[i]);
+    FV<V> d = unpackv<V>(dy[i]);
+    const FV<V> yv = unpackv<V>(y[i]);
 #pragma unroll
-    for (int k = 0; k < 8; ++k)
+    for (int k = 0; k < V; ++k)
       if (!(yv.v[k] > 0.f)) d.v[k] = 0.f;
-    dx[i] = pack8(d);
+    dx[i] = packv<V>(d);
   }
 }
 
 // out = a + b  (bf16 vectors)
+template <int V>
 __global__ void add_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b,
                            uint4* __restrict__ o, long long n16) {
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16;
        i += (long long)gridDim.x * blockDim.x) {
-    F8 x = unpack8(a[i]);
-    const F8 y = unpack8(b[i]);
+    FV<V> x = unpackv<V>(a[i]);
+    const FV<V> y = unpackv<V>(b[i]);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) x.v[k] += y.v[k];
-    o[i] = pack8(x);
+    for (int k = 0; k < V; ++k) x.v[k] += y.v[k];
+    o[i] = packv<V>(x);
   }
 }
 
 // a[..., :Gb] += b  (channel-prefix add: the gradient of PyramidNet's zero-padded shortcut)
+template <int V>
 __global__ void add_prefix_kernel(uint4* __restrict__ a, const uint4* __restrict__ b, long long P,
                                   int Ga, int Gb) {
   const long long total = P * Gb;
@@ -490,11 +520,11 @@ __global__ void add_prefix_kernel(uint4* __restrict__ a, const uint4* __restrict
        i += (long long)gridDim.x * blockDim.x) {
     const int g = (int)(i % Gb);
     const long long p = i / Gb;
-    F8 x = unpack8(a[p * Ga + g]);
-    const F8 y = unpack8(b[i]);
+    FV<V> x = unpackv<V>(a[p * Ga + g]);
+    const FV<V> y = unpackv<V>(b[i]);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) x.v[k] += y.v[k];
-    a[p * Ga + g] = pack8(x);
+    for (int k = 0; k < V; ++k) x.v[k] += y.v[k];
+    a[p * Ga + g] = packv<V>(x);
   }
 }
 
@@ -503,6 +533,7 @@ __global__ void add_prefix_kernel(uint4* __restrict__ a, const uint4* __restrict
 // ceil-mode windows overhang; the reference's AvgPool2d(2, stride=2,
 // ceil_mode=True) on even sizes never overhangs), mode 1 = max.
 // ---------------------------------------------------------------------------
+template <int V>
 __global__ void pool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int N, int H,
                                 int W, int Ho, int Wo, int G, int k, int stride, int pad, int mode) {
   const long long total = (long long)N * Ho * Wo * G;
@@ -514,9 +545,9 @@ __global__ void pool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__
     t /= Wo;
     const int ho = (int)(t % Ho);
     const long long n = t / Ho;
-    F8 acc;
+    FV<V> acc;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) acc.v[q] = mode ? -3.0e38f : 0.f;
+    for (int q = 0; q < V; ++q) acc.v[q] = mode ? -3.0e38f : 0.f;
     int cnt = 0;
     for (int r = 0; r < k; ++r) {
       const int h = ho * stride - pad + r;
@@ -524,22 +555,23 @@ __global__ void pool_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__
       for (int s = 0; s < k; ++s) {
         const int w = wo * stride - pad + s;
         if (w < 0 || w >= W) continue;
-        const F8 v = unpack8(x[((n * H + h) * W + w) * G + g]);
+        const FV<V> v = unpackv<V>(x[((n * H + h) * W + w) * G + g]);
         ++cnt;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) acc.v[q] = mode ? fmaxf(acc.v[q], v.v[q]) : acc.v[q] + v.v[q];
+        for (int q = 0; q < V; ++q) acc.v[q] = mode ? fmaxf(acc.v[q], v.v[q]) : acc.v[q] + v.v[q];
       }
     }
     if (!mode) {
       const float inv = cnt > 0 ? 1.f / (float)cnt : 0.f;
 #pragma unroll
-      for (int q = 0; q < 8; ++q) acc.v[q] *= inv;
+      for (int q = 0; q < V; ++q) acc.v[q] *= inv;
     }
-    y[i] = pack8(acc);
+    y[i] = packv<V>(acc);
   }
 }
 
 // Gather-form backward (no atomics): each input element sums the windows it belongs to.
+template <int V>
 __global__ void pool_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x,
                                 const uint4* __restrict__ y, uint4* __restrict__ dx, int N, int H,
                                 int W, int Ho, int Wo, int G, int k, int stride, int pad, int mode) {
@@ -552,11 +584,11 @@ __global__ void pool_bwd_kernel(const uint4* __restrict__ dy, const uint4* __res
     t /= W;
     const int h = (int)(t % H);
     const long long n = t / H;
-    F8 acc;
+    FV<V> acc;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) acc.v[q] = 0.f;
-    F8 xv;
-    if (mode) xv = unpack8(x[i]);
+    for (int q = 0; q < V; ++q) acc.v[q] = 0.f;
+    FV<V> xv;
+    if (mode) xv = unpackv<V>(x[i]);
     for (int ho = 0; ho < Ho; ++ho) {
       const int r = h - (ho * stride - pad);
       if (r < 0 || r >= k) continue;
@@ -564,14 +596,14 @@ __global__ void pool_bwd_kernel(const uint4* __restrict__ dy, const uint4* __res
         const int s = w - (wo * stride - pad);
         if (s < 0 || s >= k) continue;
         const long long oi = ((n * Ho + ho) * Wo + wo) * G + g;
-        const F8 d = unpack8(dy[oi]);
+        const FV<V> d = unpackv<V>(dy[oi]);
         if (mode) {
           // torch routes the gradient to the FIRST maximum of the window (row-major scan);
           // bf16 data ties often, so check that no earlier tap holds the same value.
-          const F8 yv = unpack8(y[oi]);
-          bool mine[8];
+          const FV<V> yv = unpackv<V>(y[oi]);
+          bool mine[V];
 #pragma unroll
-          for (int q = 0; q < 8; ++q) mine[q] = xv.v[q] == yv.v[q];
+          for (int q = 0; q < V; ++q) mine[q] = xv.v[q] == yv.v[q];
           for (int rr = 0; rr <= r; ++rr) {
             const int hh = ho * stride - pad + rr;
             if (hh < 0 || hh >= H) continue;
@@ -579,14 +611,14 @@ __global__ void pool_bwd_kernel(const uint4* __restrict__ dy, const uint4* __res
             for (int sc = 0; sc < s_end; ++sc) {
               const int ww = wo * stride - pad + sc;
               if (ww < 0 || ww >= W) continue;
-              const F8 ev = unpack8(x[((n * H + hh) * W + ww) * G + g]);
+              const FV<V> ev = unpackv<V>(x[((n * H + hh) * W + ww) * G + g]);
 #pragma unroll
-              for (int q = 0; q < 8; ++q)
+              for (int q = 0; q < V; ++q)
                 if (ev.v[q] == yv.v[q]) mine[q] = false;
             }
           }
 #pragma unroll
-          for (int q = 0; q < 8; ++q)
+          for (int q = 0; q < V; ++q)
             if (mine[q]) acc.v[q] += d.v[q];
         } else {
           int hs = ho * stride - pad, ws = wo * stride - pad;
@@ -595,15 +627,16 @@ __global__ void pool_bwd_kernel(const uint4* __restrict__ dy, const uint4* __res
           ws = ws < 0 ? 0 : ws;
           const float inv = 1.f / (float)((he - hs) * (we - ws));
 #pragma unroll
-          for (int q = 0; q < 8; ++q) acc.v[q] += d.v[q] * inv;
+          for (int q = 0; q < V; ++q) acc.v[q] += d.v[q] * inv;
         }
       }
     }
-    dx[i] = pack8(acc);
+    dx[i] = packv<V>(acc);
   }
 }
 
 // y[n,ho,wo] = x[n, 2ho, 2wo]   and its adjoint (zero insertion)
+template <int V>
 __global__ void subsample2_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int N, int H,
                                   int W, int Ho, int Wo, int G, int adjoint) {
   if (!adjoint) {
@@ -638,6 +671,7 @@ __global__ void subsample2_kernel(const uint4* __restrict__ x, uint4* __restrict
 }
 
 // Global average pool [N,HW,Cp] -> [N,Cp] and its backward (broadcast / HW).
+template <int V>
 __global__ void gap_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int N, int HW,
                                int G) {
   const long long total = (long long)N * G;
@@ -645,20 +679,21 @@ __global__ void gap_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ 
        i += (long long)gridDim.x * blockDim.x) {
     const int g = (int)(i % G);
     const long long n = i / G;
-    F8 acc;
+    FV<V> acc;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) acc.v[q] = 0.f;
+    for (int q = 0; q < V; ++q) acc.v[q] = 0.f;
     for (int p = 0; p < HW; ++p) {
-      const F8 v = unpack8(x[(n * HW + p) * G + g]);
+      const FV<V> v = unpackv<V>(x[(n * HW + p) * G + g]);
 #pragma unroll
-      for (int q = 0; q < 8; ++q) acc.v[q] += v.v[q];
+      for (int q = 0; q < V; ++q) acc.v[q] += v.v[q];
     }
     const float inv = 1.f / (float)HW;
 #pragma unroll
-    for (int q = 0; q < 8; ++q) acc.v[q] *= inv;
-    y[i] = pack8(acc);
+    for (int q = 0; q < V; ++q) acc.v[q] *= inv;
+    y[i] = packv<V>(acc);
   }
 }
+template <int V>
 __global__ void gap_bwd_kernel(const uint4* __restrict__ dy, uint4* __restrict__ dx, int N, int HW,
                                int G) {
   const long long total = (long long)N * HW * G;
@@ -667,10 +702,10 @@ __global__ void gap_bwd_kernel(const uint4* __restrict__ dy, uint4* __restrict__
        i += (long long)gridDim.x * blockDim.x) {
     const int g = (int)(i % G);
     const long long n = i / ((long long)HW * G);
-    F8 d = unpack8(dy[n * G + g]);
+    FV<V> d = unpackv<V>(dy[n * G + g]);
 #pragma unroll
-    for (int q = 0; q < 8; ++q) d.v[q] *= inv;
-    dx[i] = pack8(d);
+    for (int q = 0; q < V; ++q) d.v[q] *= inv;
+    dx[i] = packv<V>(d);
   }
 }
 
@@ -724,49 +759,123 @@ __global__ void softmax_ce_kernel(const float* __restrict__ logits, const long l
 }
 
 // Column sum of a bf16 [P][Cp] matrix into fp32 out[C] (bias gradients).
+template <int V>
 __global__ void colsum_kernel(const uint4* __restrict__ x, float* __restrict__ out, long long P,
                               int C, int G) {
-  extern __shared__ float red[];  // [rows][G][8]
+  extern __shared__ float red[];  // [rows][G][V]
   const int rows = blockDim.x / G;
   const int g = threadIdx.x % G, rrow = threadIdx.x / G;
-  float s[8];
+  float s[V];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) s[k] = 0.f;
+  for (int k = 0; k < V; ++k) s[k] = 0.f;
   for (long long p = (long long)blockIdx.x * rows + rrow; p < P; p += (long long)gridDim.x * rows) {
-    const F8 f = unpack8(x[p * G + g]);
+    const FV<V> f = unpackv<V>(x[p * G + g]);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) s[k] += f.v[k];
+    for (int k = 0; k < V; ++k) s[k] += f.v[k];
   }
 #pragma unroll
-  for (int k = 0; k < 8; ++k) red[(size_t)threadIdx.x * 8 + k] = s[k];
+  for (int k = 0; k < V; ++k) red[(size_t)threadIdx.x * V + k] = s[k];
   __syncthreads();
-  for (int o = threadIdx.x; o < G * 8; o += blockDim.x) {
-    const int og = o / 8, ok = o % 8;
+  for (int o = threadIdx.x; o < G * V; o += blockDim.x) {
+    const int og = o / V, ok = o % V;
     float acc = 0.f;
-    for (int rr = 0; rr < rows; ++rr) acc += red[((size_t)rr * G + og) * 8 + ok];
-    if (og * 8 + ok < C) atomicAdd(&out[og * 8 + ok], acc);
+    for (int rr = 0; rr < rows; ++rr) acc += red[((size_t)rr * G + og) * V + ok];
+    if (og * V + ok < C) atomicAdd(&out[og * V + ok], acc);
   }
 }
 
-// fp32 [rows][cols] -> bf16 [rows][cols_p] (zero padded) and back
-__global__ void f32_to_bf16_pad_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y,
-                                       long long rows, int cols, int cols_p) {
+// fp32 [rows][cols] -> activation type [rows][cols_p] (zero padded) and back
+template <typename T>
+__device__ __forceinline__ T from_f32(float v);
+template <>
+__device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) {
+  return __float2bfloat16(v);
+}
+template <>
+__device__ __forceinline__ float from_f32<float>(float v) {
+  return v;
+}
+__device__ __forceinline__ float to_f32v(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float to_f32v(float v) { return v; }
+
+template <typename T>
+__global__ void pad_cast_kernel(const float* __restrict__ x, T* __restrict__ y, long long rows, int cols,
+                                int cols_p) {
   const long long total = rows * cols_p;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int c = (int)(i % cols_p);
     const long long r = i / cols_p;
-    y[i] = __float2bfloat16(c < cols ? x[r * cols + c] : 0.f);
+    y[i] = from_f32<T>(c < cols ? x[r * cols + c] : 0.f);
   }
 }
-__global__ void bf16_to_f32_unpad_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ y,
-                                         long long rows, int cols, int cols_p) {
+template <typename T>
+__global__ void unpad_cast_kernel(const T* __restrict__ x, float* __restrict__ y, long long rows, int cols,
+                                  int cols_p) {
   const long long total = rows * cols;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
     const int c = (int)(i % cols);
     const long long r = i / cols;
-    y[i] = __bfloat162float(x[r * cols_p + c]);
+    y[i] = to_f32v(x[r * cols_p + c]);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// fp32 Linear on CUDA cores (fp32 activation mode only).  The reference's nn.Linear runs in full
+// fp32 (torch keeps TF32 off for matmuls by default: pytorch/model.py:77,111), so in the
+// matched-precision mode the fully connected layers do not go through the TF32 tensor-core path.
+// The layers this serves are small (271 -> 10 in PyramidNet); one thread per output element with
+// float4 loads along K is enough.
+//   fwd  : y[n][o]  = [relu](sum_k x[n][k] w[o][k] + b[o])         x [N][Kp], y [N][Op] (pads 0)
+//   dgrad: dx[n][k] = sum_o dy[n][o] w[o][k]
+//   wgrad: dw[o][k] (+)= sum_n dy[n][o] x[n][k]
+// ---------------------------------------------------------------------------
+__global__ void linear_f32_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
+                                      const float* __restrict__ bias, float* __restrict__ y, int N,
+                                      int K, int Kp, int O, int Op, int relu) {
+  const long long total = (long long)N * Op;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int o = (int)(i % Op);
+    const long long n = i / Op;
+    float acc = 0.f;
+    if (o < O) {
+      const float* xr = x + n * Kp;
+      const float* wr = w + (long long)o * K;
+      for (int k = 0; k < K; ++k) acc = fmaf(xr[k], wr[k], acc);
+      if (bias != nullptr) acc += bias[o];
+      if (relu) acc = fmaxf(acc, 0.f);
+    }
+    y[i] = acc;
+  }
+}
+__global__ void linear_f32_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w,
+                                        float* __restrict__ dx, int N, int K, int Kp, int O, int Op) {
+  const long long total = (long long)N * Kp;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i % Kp);
+    const long long n = i / Kp;
+    float acc = 0.f;
+    if (k < K) {
+      const float* dr = dy + n * Op;
+      for (int o = 0; o < O; ++o) acc = fmaf(dr[o], w[(long long)o * K + k], acc);
+    }
+    dx[i] = acc;
+  }
+}
+__global__ void linear_f32_wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                        float* __restrict__ dw, int N, int K, int Kp, int O, int Op,
+                                        int accumulate) {
+  const long long total = (long long)O * K;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i % K);
+    const int o = (int)(i / K);
+    float acc = 0.f;
+    for (int n = 0; n < N; ++n) acc = fmaf(dy[(long long)n * Op + o], x[(long long)n * Kp + k], acc);
+    dw[i] = accumulate ? dw[i] + acc : acc;
   }
 }
 
@@ -776,47 +885,69 @@ using namespace dtdl;
 #define STREAM(s) reinterpret_cast<cudaStream_t>(s)
 static const int kMaxBlocks = 148 * 8;
 
-extern "C" int dtdl_nchw_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, int Cp,
-                                      void* stream) {
+// act -> channels per 16-byte vector
+#define DTDL_ACT_OK(act) DTDL_REQUIRE((act) == kActBf16 || (act) == kActF32, "act must be 0 (bf16) or 1 (fp32)")
+static inline int vec_of(int act) { return act == kActF32 ? 4 : 8; }
+// launches KERNEL<8> (bf16) or KERNEL<4> (fp32) with the same configuration and arguments
+#define LAUNCH_ACT(act, KERNEL, grid, block, smem, stream, ...)              \
+  do {                                                                         \
+    if ((act) == kActF32)                                                      \
+      KERNEL<4><<<(grid), (block), (smem), STREAM(stream)>>>(__VA_ARGS__);     \
+    else                                                                       \
+      KERNEL<8><<<(grid), (block), (smem), STREAM(stream)>>>(__VA_ARGS__);     \
+    DTDL_CHECK_CUDA(cudaGetLastError());                                       \
+  } while (0)
+
+extern "C" int dtdl_nchw_to_nhwc(const float* x, void* y, int N, int C, int H, int W, int Cp, int act,
+                                 void* stream) {
+  DTDL_ACT_OK(act);
   DTDL_REQUIRE(Cp % 8 == 0 && Cp >= C, "bad channel padding");
-  const int G = Cp / 8;
+  const int G = Cp / vec_of(act);
   const long long total = (long long)N * H * W * G;
-  nchw_to_nhwc_kernel<<<grid_for(total, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
-      x, reinterpret_cast<uint4*>(y), N, C, H * W, G);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  LAUNCH_ACT(act, nchw_to_nhwc_kernel, grid_for(total, 256, kMaxBlocks), 256, 0, stream, x,
+             reinterpret_cast<uint4*>(y), N, C, H * W, G);
   return 0;
 }
 
-extern "C" int dtdl_nchw_to_s2d_bf16(const float* x, void* y, int N, int C, int H, int W, int Cp,
-                                     void* stream) {
+extern "C" int dtdl_nchw_to_s2d(const float* x, void* y, int N, int C, int H, int W, int Cp, int act,
+                                void* stream) {
+  DTDL_ACT_OK(act);
   DTDL_REQUIRE(Cp % 8 == 0 && Cp >= 4 * C && H % 2 == 0 && W % 2 == 0, "bad space-to-depth shape");
-  const int G = Cp / 8;
+  const int G = Cp / vec_of(act);
   const long long total = (long long)N * (H / 2) * (W / 2) * G;
-  nchw_to_s2d_kernel<<<grid_for(total, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
-      x, reinterpret_cast<uint4*>(y), N, C, H, W, G);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  LAUNCH_ACT(act, nchw_to_s2d_kernel, grid_for(total, 256, kMaxBlocks), 256, 0, stream, x,
+             reinterpret_cast<uint4*>(y), N, C, H, W, G);
   return 0;
 }
 
-extern "C" int dtdl_bn_stats(const void* x, float* sums, long long P, int Cp, void* stream) {
-  DTDL_REQUIRE(Cp % 8 == 0 && Cp <= 8192, "bad channel padding");
-  const int G = Cp / 8;
-  const int block = block_for_groups(G);
-  const int rows = block / G;
-  const size_t smem = (size_t)block * 16 * sizeof(float);
+// One-time opt-in to large dynamic shared memory for the reduction kernels of both instantiations.
+static int set_reduce_attrs() {
   static bool attr[64] = {false};
   int dev = 0;
   DTDL_CHECK_CUDA(cudaGetDevice(&dev));
   if (!attr[dev & 63]) {
-    DTDL_CHECK_CUDA(
-        cudaFuncSetAttribute(bn_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
-    DTDL_CHECK_CUDA(cudaFuncSetAttribute(bn_bwd_reduce_kernel,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(bn_stats_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(bn_stats_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(bn_bwd_reduce_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(bn_bwd_reduce_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(bn_apply_stats_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 131072));
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(bn_apply_stats_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 131072));
     attr[dev & 63] = true;
   }
-  bn_stats_kernel<<<grid_for(P, rows * 8, 148 * 4), block, smem, STREAM(stream)>>>(
-      reinterpret_cast<const uint4*>(x), sums, P, G);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int dtdl_bn_stats(const void* x, float* sums, long long P, int Cp, int act, void* stream) {
+  DTDL_ACT_OK(act);
+  const int V = vec_of(act);
+  DTDL_REQUIRE(Cp % 8 == 0 && Cp / V <= 1024, "bad channel padding");
+  const int G = Cp / V;
+  const int block = block_for_groups(G);
+  const int rows = block / G;
+  const size_t smem = (size_t)block * 2 * V * sizeof(float);
+  if (set_reduce_attrs()) return 1;
+  LAUNCH_ACT(act, bn_stats_kernel, grid_for(P, rows * 8, 148 * 4), block, smem, stream,
+             reinterpret_cast<const uint4*>(x), sums, P, G);
   return 0;
 }
 
@@ -825,10 +956,10 @@ extern "C" int dtdl_bn_apply(const void* x, void* y, const float* sums, const fl
                              long long* num_batches_tracked, float* save_mean, float* save_rstd,
                              const void* residual, int Cres_p, long long P, int C, int Cp, float eps,
                              float momentum, int relu, int training, float* zero_buf, int zero_n,
-                             void* stream) {
+                             int act, void* stream) {
   return dtdl_bn_apply_stats(x, y, sums, gamma, beta, running_mean, running_var, num_batches_tracked,
                              save_mean, save_rstd, residual, Cres_p, P, C, Cp, eps, momentum, relu,
-                             training, zero_buf, zero_n, nullptr, stream);
+                             training, zero_buf, zero_n, nullptr, act, stream);
 }
 
 extern "C" int dtdl_bn_apply_stats(const void* x, void* y, const float* sums, const float* gamma,
@@ -836,7 +967,9 @@ extern "C" int dtdl_bn_apply_stats(const void* x, void* y, const float* sums, co
                                    long long* num_batches_tracked, float* save_mean, float* save_rstd,
                                    const void* residual, int Cres_p, long long P, int C, int Cp,
                                    float eps, float momentum, int relu, int training, float* zero_buf,
-                                   int zero_n, float* out_sums, void* stream) {
+                                   int zero_n, float* out_sums, int act, void* stream) {
+  DTDL_ACT_OK(act);
+  const int V = vec_of(act);
   DTDL_REQUIRE(Cp % 8 == 0 && Cres_p % 8 == 0 && Cres_p <= Cp, "bad channel padding");
   BnApplyArgs a;
   a.x = reinterpret_cast<const uint4*>(x);
@@ -850,10 +983,10 @@ extern "C" int dtdl_bn_apply_stats(const void* x, void* y, const float* sums, co
   a.save_mean = save_mean;
   a.save_rstd = save_rstd;
   a.residual = reinterpret_cast<const uint4*>(residual);
-  a.Gres = Cres_p / 8;
+  a.Gres = Cres_p / V;
   a.P = P;
   a.C = C;
-  a.G = Cp / 8;
+  a.G = Cp / V;
   a.eps = eps;
   a.momentum = momentum;
   a.relu = relu;
@@ -862,55 +995,46 @@ extern "C" int dtdl_bn_apply_stats(const void* x, void* y, const float* sums, co
   a.zero_n = zero_n;
   a.out_sums = out_sums;
   if (out_sums != nullptr) {
-    DTDL_REQUIRE(Cp <= 8192, "bad channel padding");
+    DTDL_REQUIRE(a.G <= 1024, "bad channel padding");
     const int block = block_for_groups(a.G);
     const int rows = block / a.G;
-    const size_t smem = (size_t)(2 * Cp + block * 16) * sizeof(float);
-    static bool attr[64] = {false};
-    int dev = 0;
-    DTDL_CHECK_CUDA(cudaGetDevice(&dev));
-    if (!attr[dev & 63]) {
-      DTDL_CHECK_CUDA(cudaFuncSetAttribute(bn_apply_stats_kernel,
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, 131072));
-      attr[dev & 63] = true;
-    }
-    bn_apply_stats_kernel<<<grid_for(P, rows * 4, kMaxBlocks), block, smem, STREAM(stream)>>>(a);
-    DTDL_CHECK_CUDA(cudaGetLastError());
+    const size_t smem = (size_t)(2 * Cp + block * 2 * V) * sizeof(float);
+    if (set_reduce_attrs()) return 1;
+    LAUNCH_ACT(act, bn_apply_stats_kernel, grid_for(P, rows * 4, kMaxBlocks), block, smem, stream, a);
     return 0;
   }
   const long long total = P * a.G;
-  bn_apply_kernel<<<grid_for(total, 256 * 4, kMaxBlocks), 256, 2 * Cp * sizeof(float),
-                    STREAM(stream)>>>(a);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  LAUNCH_ACT(act, bn_apply_kernel, grid_for(total, 256 * 4, kMaxBlocks), 256, 2 * Cp * sizeof(float), stream, a);
   return 0;
 }
 
 extern "C" int dtdl_bn_bwd(const void* dy, const void* x, const void* y, const float* save_mean,
                            const float* save_rstd, const float* gamma, float* sums2, void* dx,
                            void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
-                           long long P, int C, int Cp, int relu, float* zero_buf, int zero_n,
+                           long long P, int C, int Cp, int relu, float* zero_buf, int zero_n, int act,
                            void* stream) {
   return dtdl_bn_bwd_add(dy, x, y, save_mean, save_rstd, gamma, sums2, dx, dres, Cres_p, dgamma, dbeta,
-                         accumulate, P, C, Cp, relu, zero_buf, zero_n, nullptr, stream);
+                         accumulate, P, C, Cp, relu, zero_buf, zero_n, nullptr, act, stream);
 }
 
 extern "C" int dtdl_bn_bwd_add(const void* dy, const void* x, const void* y, const float* save_mean,
-                           const float* save_rstd, const float* gamma, float* sums2, void* dx,
-                           void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
-                           long long P, int C, int Cp, int relu, float* zero_buf, int zero_n,
-                           const void* add_in,
-                               void* stream) {
-  DTDL_REQUIRE(Cp % 8 == 0 && Cres_p % 8 == 0 && Cres_p <= Cp && Cp <= 8192, "bad channel padding");
+                               const float* save_rstd, const float* gamma, float* sums2, void* dx,
+                               void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
+                               long long P, int C, int Cp, int relu, float* zero_buf, int zero_n,
+                               const void* add_in, int act, void* stream) {
+  DTDL_ACT_OK(act);
+  const int V = vec_of(act);
+  DTDL_REQUIRE(Cp % 8 == 0 && Cres_p % 8 == 0 && Cres_p <= Cp && Cp / V <= 1024, "bad channel padding");
   DTDL_REQUIRE(!relu || y != nullptr, "relu backward needs the saved output");
-  const int G = Cp / 8;
+  const int G = Cp / V;
   {
     const int block = block_for_groups(G);
     const int rows = block / G;
-    const size_t smem = (size_t)block * 16 * sizeof(float);
-    bn_bwd_reduce_kernel<<<grid_for(P, rows * 8, 148 * 4), block, smem, STREAM(stream)>>>(
-        reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(x),
-        reinterpret_cast<const uint4*>(y), save_mean, save_rstd, sums2, P, C, G, relu);
-    DTDL_CHECK_CUDA(cudaGetLastError());
+    const size_t smem = (size_t)block * 2 * V * sizeof(float);
+    if (set_reduce_attrs()) return 1;
+    LAUNCH_ACT(act, bn_bwd_reduce_kernel, grid_for(P, rows * 8, 148 * 4), block, smem, stream,
+               reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(x),
+               reinterpret_cast<const uint4*>(y), save_mean, save_rstd, sums2, P, C, G, relu);
   }
   BnBwdArgs a;
   a.dy = reinterpret_cast<const uint4*>(dy);
@@ -922,7 +1046,7 @@ extern "C" int dtdl_bn_bwd_add(const void* dy, const void* x, const void* y, con
   a.sums2 = sums2;
   a.dx = reinterpret_cast<uint4*>(dx);
   a.dres = reinterpret_cast<uint4*>(dres);
-  a.Gres = Cres_p / 8;
+  a.Gres = Cres_p / V;
   a.dgamma = dgamma;
   a.dbeta = dbeta;
   a.accumulate = accumulate;
@@ -934,92 +1058,95 @@ extern "C" int dtdl_bn_bwd_add(const void* dy, const void* x, const void* y, con
   a.zero_n = zero_n;
   a.add_in = reinterpret_cast<const uint4*>(add_in);
   const long long total = P * G;
-  bn_bwd_apply_kernel<<<grid_for(total, 256 * 4, kMaxBlocks), 256, 5 * Cp * sizeof(float),
-                        STREAM(stream)>>>(a);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  LAUNCH_ACT(act, bn_bwd_apply_kernel, grid_for(total, 256 * 4, kMaxBlocks), 256, 5 * Cp * sizeof(float),
+             stream, a);
   return 0;
 }
 
-extern "C" int dtdl_relu_bwd(const void* dy, const void* y, void* dx, long long n_elems,
+extern "C" int dtdl_relu_bwd(const void* dy, const void* y, void* dx, long long n_elems, int act,
                              void* stream) {
+  DTDL_ACT_OK(act);
   DTDL_REQUIRE(n_elems % 8 == 0, "element count must be a multiple of 8");
-  const long long n16 = n_elems / 8;
-  relu_bwd_kernel<<<grid_for(n16, 256 * 4, kMaxBlocks), 256, 0, STREAM(stream)>>>(
-      reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),
-      reinterpret_cast<uint4*>(dx), n16);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  const long long n16 = n_elems / vec_of(act);
+  LAUNCH_ACT(act, relu_bwd_kernel, grid_for(n16, 256 * 4, kMaxBlocks), 256, 0, stream,
+             reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(y),
+             reinterpret_cast<uint4*>(dx), n16);
   return 0;
 }
 
-extern "C" int dtdl_add_bf16(const void* a, const void* b, void* out, long long n_elems,
-                             void* stream) {
+extern "C" int dtdl_add(const void* a, const void* b, void* out, long long n_elems, int act,
+                        void* stream) {
+  DTDL_ACT_OK(act);
   DTDL_REQUIRE(n_elems % 8 == 0, "element count must be a multiple of 8");
-  const long long n16 = n_elems / 8;
-  add_kernel<<<grid_for(n16, 256 * 4, kMaxBlocks), 256, 0, STREAM(stream)>>>(
-      reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b),
-      reinterpret_cast<uint4*>(out), n16);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  const long long n16 = n_elems / vec_of(act);
+  LAUNCH_ACT(act, add_kernel, grid_for(n16, 256 * 4, kMaxBlocks), 256, 0, stream,
+             reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b),
+             reinterpret_cast<uint4*>(out), n16);
   return 0;
 }
 
-extern "C" int dtdl_add_prefix_bf16(void* a, const void* b, long long P, int Ca_p, int Cb_p,
-                                    void* stream) {
+extern "C" int dtdl_add_prefix(void* a, const void* b, long long P, int Ca_p, int Cb_p, int act,
+                               void* stream) {
+  DTDL_ACT_OK(act);
+  const int V = vec_of(act);
   DTDL_REQUIRE(Ca_p % 8 == 0 && Cb_p % 8 == 0 && Cb_p <= Ca_p, "bad channel padding");
-  add_prefix_kernel<<<grid_for(P * (Cb_p / 8), 256 * 4, kMaxBlocks), 256, 0, STREAM(stream)>>>(
-      reinterpret_cast<uint4*>(a), reinterpret_cast<const uint4*>(b), P, Ca_p / 8, Cb_p / 8);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  LAUNCH_ACT(act, add_prefix_kernel, grid_for(P * (Cb_p / V), 256 * 4, kMaxBlocks), 256, 0, stream,
+             reinterpret_cast<uint4*>(a), reinterpret_cast<const uint4*>(b), P, Ca_p / V, Cb_p / V);
   return 0;
 }
 
 extern "C" int dtdl_pool_fwd(const void* x, void* y, int N, int H, int W, int Ho, int Wo, int Cp,
-                             int k, int stride, int pad, int mode, void* stream) {
+                             int k, int stride, int pad, int mode, int act, void* stream) {
+  DTDL_ACT_OK(act);
   DTDL_REQUIRE(Cp % 8 == 0, "bad channel padding");
-  const long long total = (long long)N * Ho * Wo * (Cp / 8);
-  pool_fwd_kernel<<<grid_for(total, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
-      reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(y), N, H, W, Ho, Wo, Cp / 8, k,
-      stride, pad, mode);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  const int G = Cp / vec_of(act);
+  const long long total = (long long)N * Ho * Wo * G;
+  LAUNCH_ACT(act, pool_fwd_kernel, grid_for(total, 256, kMaxBlocks), 256, 0, stream,
+             reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(y), N, H, W, Ho, Wo, G, k,
+             stride, pad, mode);
   return 0;
 }
 
 extern "C" int dtdl_pool_bwd(const void* dy, const void* x, const void* y, void* dx, int N, int H,
                              int W, int Ho, int Wo, int Cp, int k, int stride, int pad, int mode,
-                             void* stream) {
+                             int act, void* stream) {
+  DTDL_ACT_OK(act);
   DTDL_REQUIRE(Cp % 8 == 0, "bad channel padding");
-  const long long total = (long long)N * H * W * (Cp / 8);
-  pool_bwd_kernel<<<grid_for(total, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
-      reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(x),
-      reinterpret_cast<const uint4*>(y), reinterpret_cast<uint4*>(dx), N, H, W, Ho, Wo, Cp / 8, k,
-      stride, pad, mode);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  const int G = Cp / vec_of(act);
+  const long long total = (long long)N * H * W * G;
+  LAUNCH_ACT(act, pool_bwd_kernel, grid_for(total, 256, kMaxBlocks), 256, 0, stream,
+             reinterpret_cast<const uint4*>(dy), reinterpret_cast<const uint4*>(x),
+             reinterpret_cast<const uint4*>(y), reinterpret_cast<uint4*>(dx), N, H, W, Ho, Wo, G, k,
+             stride, pad, mode);
   return 0;
 }
 
 extern "C" int dtdl_subsample2(const void* x, void* y, int N, int H, int W, int Cp, int adjoint,
-                               void* stream) {
+                               int act, void* stream) {
+  DTDL_ACT_OK(act);
   DTDL_REQUIRE(Cp % 8 == 0, "bad channel padding");
+  const int G = Cp / vec_of(act);
   const int Ho = (H + 1) / 2, Wo = (W + 1) / 2;
-  const long long total = (long long)N * (adjoint ? H * W : Ho * Wo) * (Cp / 8);
-  subsample2_kernel<<<grid_for(total, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
-      reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(y), N, H, W, Ho, Wo, Cp / 8,
-      adjoint);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  const long long total = (long long)N * (adjoint ? H * W : Ho * Wo) * G;
+  LAUNCH_ACT(act, subsample2_kernel, grid_for(total, 256, kMaxBlocks), 256, 0, stream,
+             reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(y), N, H, W, Ho, Wo, G, adjoint);
   return 0;
 }
 
-extern "C" int dtdl_gap_fwd(const void* x, void* y, int N, int HW, int Cp, void* stream) {
+extern "C" int dtdl_gap_fwd(const void* x, void* y, int N, int HW, int Cp, int act, void* stream) {
+  DTDL_ACT_OK(act);
   DTDL_REQUIRE(Cp % 8 == 0, "bad channel padding");
-  gap_fwd_kernel<<<grid_for((long long)N * (Cp / 8), 64, kMaxBlocks), 64, 0, STREAM(stream)>>>(
-      reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(y), N, HW, Cp / 8);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  const int G = Cp / vec_of(act);
+  LAUNCH_ACT(act, gap_fwd_kernel, grid_for((long long)N * G, 64, kMaxBlocks), 64, 0, stream,
+             reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(y), N, HW, G);
   return 0;
 }
-extern "C" int dtdl_gap_bwd(const void* dy, void* dx, int N, int HW, int Cp, void* stream) {
+extern "C" int dtdl_gap_bwd(const void* dy, void* dx, int N, int HW, int Cp, int act, void* stream) {
+  DTDL_ACT_OK(act);
   DTDL_REQUIRE(Cp % 8 == 0, "bad channel padding");
-  gap_bwd_kernel<<<grid_for((long long)N * HW * (Cp / 8), 256, kMaxBlocks), 256, 0,
-                   STREAM(stream)>>>(reinterpret_cast<const uint4*>(dy),
-                                     reinterpret_cast<uint4*>(dx), N, HW, Cp / 8);
-  DTDL_CHECK_CUDA(cudaGetLastError());
+  const int G = Cp / vec_of(act);
+  LAUNCH_ACT(act, gap_bwd_kernel, grid_for((long long)N * HW * G, 256, kMaxBlocks), 256, 0, stream,
+             reinterpret_cast<const uint4*>(dy), reinterpret_cast<uint4*>(dx), N, HW, G);
   return 0;
 }
 
@@ -1035,28 +1162,60 @@ extern "C" int dtdl_softmax_ce(const float* logits, const long long* targets, fl
   return 0;
 }
 
-extern "C" int dtdl_colsum(const void* x, float* out, long long P, int C, int Cp, void* stream) {
-  DTDL_REQUIRE(Cp % 8 == 0 && Cp <= 8192, "bad channel padding");
-  const int G = Cp / 8;
+extern "C" int dtdl_colsum(const void* x, float* out, long long P, int C, int Cp, int act,
+                           void* stream) {
+  DTDL_ACT_OK(act);
+  const int V = vec_of(act);
+  DTDL_REQUIRE(Cp % 8 == 0 && Cp / V <= 1024, "bad channel padding");
+  const int G = Cp / V;
   const int block = block_for_groups(G);
   const int rows = block / G;
-  colsum_kernel<<<grid_for(P, rows * 8, 148 * 2), block, (size_t)block * 8 * sizeof(float),
-                  STREAM(stream)>>>(reinterpret_cast<const uint4*>(x), out, P, C, G);
+  LAUNCH_ACT(act, colsum_kernel, grid_for(P, rows * 8, 148 * 2), block, (size_t)block * V * sizeof(float),
+             stream, reinterpret_cast<const uint4*>(x), out, P, C, G);
+  return 0;
+}
+
+extern "C" int dtdl_pad_cast(const float* x, void* y, long long rows, int cols, int cols_p, int act,
+                             void* stream) {
+  DTDL_ACT_OK(act);
+  const int grid = grid_for(rows * cols_p, 256, kMaxBlocks);
+  if (act == kActF32)
+    pad_cast_kernel<float><<<grid, 256, 0, STREAM(stream)>>>(x, reinterpret_cast<float*>(y), rows, cols, cols_p);
+  else
+    pad_cast_kernel<__nv_bfloat16><<<grid, 256, 0, STREAM(stream)>>>(x, reinterpret_cast<__nv_bfloat16*>(y),
+                                                                     rows, cols, cols_p);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int dtdl_unpad_cast(const void* x, float* y, long long rows, int cols, int cols_p, int act,
+                               void* stream) {
+  DTDL_ACT_OK(act);
+  const int grid = grid_for(rows * cols, 256, kMaxBlocks);
+  if (act == kActF32)
+    unpad_cast_kernel<float><<<grid, 256, 0, STREAM(stream)>>>(reinterpret_cast<const float*>(x), y, rows, cols, cols_p);
+  else
+    unpad_cast_kernel<__nv_bfloat16><<<grid, 256, 0, STREAM(stream)>>>(reinterpret_cast<const __nv_bfloat16*>(x),
+                                                                       y, rows, cols, cols_p);
   DTDL_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
-extern "C" int dtdl_f32_to_bf16_pad(const float* x, void* y, long long rows, int cols, int cols_p,
-                                    void* stream) {
-  f32_to_bf16_pad_kernel<<<grid_for(rows * cols_p, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
-      x, reinterpret_cast<__nv_bfloat16*>(y), rows, cols, cols_p);
+extern "C" int dtdl_linear_f32_fwd(const float* x, const float* w, const float* bias, float* y, int N,
+                                   int K, int Kp, int O, int Op, int relu, void* stream) {
+  linear_f32_fwd_kernel<<<grid_for((long long)N * Op, 128, kMaxBlocks), 128, 0, STREAM(stream)>>>(
+      x, w, bias, y, N, K, Kp, O, Op, relu);
   DTDL_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
-extern "C" int dtdl_bf16_to_f32_unpad(const void* x, float* y, long long rows, int cols, int cols_p,
-                                      void* stream) {
-  bf16_to_f32_unpad_kernel<<<grid_for(rows * cols, 256, kMaxBlocks), 256, 0, STREAM(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(x), y, rows, cols, cols_p);
+extern "C" int dtdl_linear_f32_bwd(const float* dy, const float* x, const float* w, float* dx, float* dw,
+                                   int N, int K, int Kp, int O, int Op, int accumulate, void* stream) {
+  if (dx != nullptr) {
+    linear_f32_dgrad_kernel<<<grid_for((long long)N * Kp, 128, kMaxBlocks), 128, 0, STREAM(stream)>>>(
+        dy, w, dx, N, K, Kp, O, Op);
+    DTDL_CHECK_CUDA(cudaGetLastError());
+  }
+  linear_f32_wgrad_kernel<<<grid_for((long long)O * K, 128, kMaxBlocks), 128, 0, STREAM(stream)>>>(
+      dy, x, dw, N, K, Kp, O, Op, accumulate);
   DTDL_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -1,4 +1,4 @@
-// fp32 master weights (torch OIHW / [out,in]) -> bf16 operand packs for the
+// fp32 master weights (torch OIHW / [out,in]) -> bf16 (or, in fp32 activation mode, fp32/TF32) operand packs for the
 // tcgen05 kernels, for a whole model in ONE launch (a device-side table lists
 // the layers).  Runs once per optimizer step, right after the update.  (No counterpart in the
 // reference: cuDNN reads torch's OIHW fp32 weights directly, pytorch/model.py:28-32.  The packs
@@ -17,13 +17,21 @@ namespace dtdl {
 
 struct PackEntry {
   const float* w;
-  __nv_bfloat16* wf;
-  __nv_bfloat16* wd;  // may be null (first layer needs no data gradient)
+  void* wf;
+  void* wd;  // may be null (first layer needs no data gradient)
+  int act;   // element type of the packs: 0 = bf16, 1 = fp32 (read by the tensor core as TF32)
   int Cout, Cin, taps;
   int Cin_p, Cout_p, Cin_p16, Cout_p16;
   long long f_elems, d_elems;  // elements in each pack
   long long first_block;       // prefix sum of blocks
 };
+
+__device__ __forceinline__ void pack_store(void* base, long long idx, float v, int act) {
+  if (act)
+    reinterpret_cast<float*>(base)[idx] = v;
+  else
+    reinterpret_cast<__nv_bfloat16*>(base)[idx] = __float2bfloat16(v);
+}
 
 static constexpr int kPackBlock = 256;
 static constexpr int kPackPerBlock = 256 * 8;
@@ -62,12 +70,12 @@ __device__ __forceinline__ void pack_tile(const PackEntry& e, long long tile, fl
       for (int r = w; r < kTile; r += kPackBlock / 32) {
         const int co = co0 + r;
         if (co >= e.Cout_p16) break;
-        __nv_bfloat16* dst = e.wf + (long long)co * taps * e.Cin_p + ci;
+        const long long dst = (long long)co * taps * e.Cin_p + ci;
         const float* sp = s + r * rstride + lane * taps;
 #pragma unroll
-        for (int t = 0; t < (TAPS ? TAPS : 1); ++t) dst[(long long)t * e.Cin_p] = __float2bfloat16(sp[t]);
+        for (int t = 0; t < (TAPS ? TAPS : 1); ++t) pack_store(e.wf, dst + (long long)t * e.Cin_p, sp[t], e.act);
         if (!TAPS)
-          for (int t = 1; t < taps; ++t) dst[(long long)t * e.Cin_p] = __float2bfloat16(sp[t]);
+          for (int t = 1; t < taps; ++t) pack_store(e.wf, dst + (long long)t * e.Cin_p, sp[t], e.act);
       }
     }
   }
@@ -78,12 +86,12 @@ __device__ __forceinline__ void pack_tile(const PackEntry& e, long long tile, fl
       for (int cl = w; cl < kTile; cl += kPackBlock / 32) {
         const int ci = ci0 + cl;
         if (ci >= e.Cin_p16) break;
-        __nv_bfloat16* dst = e.wd + (long long)ci * taps * e.Cout_p + co;
+        const long long dst = (long long)ci * taps * e.Cout_p + co;
         const float* sp = s + lane * rstride + cl * taps + (taps - 1);
 #pragma unroll
-        for (int t = 0; t < (TAPS ? TAPS : 1); ++t) dst[(long long)t * e.Cout_p] = __float2bfloat16(sp[-t]);
+        for (int t = 0; t < (TAPS ? TAPS : 1); ++t) pack_store(e.wd, dst + (long long)t * e.Cout_p, sp[-t], e.act);
         if (!TAPS)
-          for (int t = 1; t < taps; ++t) dst[(long long)t * e.Cout_p] = __float2bfloat16(sp[-t]);
+          for (int t = 1; t < taps; ++t) pack_store(e.wd, dst + (long long)t * e.Cout_p, sp[-t], e.act);
       }
     }
   }
@@ -137,7 +145,7 @@ pack_weights_kernel(const PackEntry* __restrict__ table, int n_entries, long lon
         const int co = (int)(r / e.taps);
         float v = 0.f;
         if (co < e.Cout && ci < e.Cin) v = e.w[((long long)co * e.Cin + ci) * e.taps + t];
-        e.wf[i] = __float2bfloat16(v);
+        pack_store(e.wf, i, v, e.act);
       } else {
         const long long j = i - e.f_elems;
         const int co = (int)(j % e.Cout_p);
@@ -147,7 +155,7 @@ pack_weights_kernel(const PackEntry* __restrict__ table, int n_entries, long lon
         float v = 0.f;
         if (co < e.Cout && ci < e.Cin)
           v = e.w[((long long)co * e.Cin + ci) * e.taps + (e.taps - 1 - t)];
-        e.wd[j] = __float2bfloat16(v);
+        pack_store(e.wd, j, v, e.act);
       }
     }
   }
@@ -162,11 +170,12 @@ extern "C" int dtdl_pack_entry_size() { return (int)sizeof(PackEntry); }
 // Fills one host-side table entry; returns the number of blocks it needs.
 extern "C" long long dtdl_pack_entry_fill(void* entry, const float* w, void* wf, void* wd, int Cout,
                                           int Cin, int taps, int Cin_p, int Cout_p,
-                                          long long first_block) {
+                                          long long first_block, int act) {
   PackEntry* e = reinterpret_cast<PackEntry*>(entry);
   e->w = w;
-  e->wf = reinterpret_cast<__nv_bfloat16*>(wf);
-  e->wd = reinterpret_cast<__nv_bfloat16*>(wd);
+  e->wf = wf;
+  e->wd = wd;
+  e->act = act ? 1 : 0;
   e->Cout = Cout;
   e->Cin = Cin;
   e->taps = taps;

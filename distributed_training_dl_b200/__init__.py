@@ -11,6 +11,7 @@ __version__ = "0.1.0"
 from . import _native  # noqa: F401
 from . import models, ops, parallel, utils  # noqa: F401
 from .engine import CrossEntropyLoss, TrainStep
+from .ops import set_precision
 from .parallel import (DataParallel, DataParallelStep, FusedAdam, FusedSGD, DistributedDataParallel, DistributedModel,
                        create_communicator, current, init, shutdown, wrap)
 from .utils import (DistributedSampler, SyntheticDataset, load_model, load_snapshot, save_model,

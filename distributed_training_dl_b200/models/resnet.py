@@ -56,13 +56,13 @@ class _StemFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, weight, op):
         N, C, H, W = x.shape
-        if op.weight is None or op.weight.device != x.device:
+        if op.weight is None or op.weight.device != x.device or op._packs_stale():
             op.weight = torch.empty((op.Cout, 12, 4, 4), dtype=torch.float32, device=x.device)
             op._alloc_packs(x.device)
             op._table = {}
         op.weight.copy_(s2d_weight(weight.detach()))
         L.pack_weights([op], op._table)
-        xs = fn.to_s2d(x)
+        xs = fn.to_s2d(x, dtype=op.act_dtype)
         y = fn.conv_fprop_raw(xs, op.wf, op.Cout_p, 4, 4, 2, out_hw=(H // 2, W // 2))
         ctx.op = op
         ctx.save_for_backward(xs, weight)
@@ -76,10 +76,11 @@ class _StemFn(torch.autograd.Function):
         N, Hs, Ws, Cin_p = xs.shape
         Ho, Wo = dy.shape[1], dy.shape[2]
         g4 = torch.empty((op.Cout, 12, 4, 4), dtype=torch.float32, device=dy.device)
-        need = nv.lib().dtdl_conv_wgrad_workspace_bytes(N, Ho, Wo, Cin_p, op.Cout_p, 4, 4)
+        act = fn.act_of(xs)
+        need = nv.lib().dtdl_conv_wgrad_workspace_bytes_ex(N, Ho, Wo, Cin_p, op.Cout_p, 4, 4, 1, act)
         ws = fn.scratch(xs.device, need)
         nv.call("conv_wgrad", nv.ptr(xs), nv.ptr(dy), nv.ptr(g4), nv.ptr(ws), ws.numel(), N, Hs, Ws, 12, Cin_p,
-                Ho, Wo, op.Cout, op.Cout_p, 4, 4, 2, 2, 0, nv.stream_ptr())
+                Ho, Wo, op.Cout, op.Cout_p, 4, 4, 2, 2, 0, 1, act, nv.stream_ptr())
         gw, acc = fn.grad_buffer(weight)
         g7 = s2d_weight_adjoint(g4)
         if acc:

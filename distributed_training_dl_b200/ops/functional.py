@@ -1,7 +1,12 @@
 """Autograd functions over the sm_100a kernels.
 
-Activation layout on the GPU: NHWC bf16, channel count padded to a multiple of 8
-(``Cp``), pad channels exactly zero.  A 2-D activation (Linear) is ``[N,1,1,Cp]``.
+Activation layout on the GPU: NHWC, channel count padded to a multiple of 8 (``Cp``), pad
+channels exactly zero.  A 2-D activation (Linear) is ``[N,1,1,Cp]``.  Two storage types,
+chosen per model (``set_precision`` / ``wrap(..., dtype=)``): ``torch.bfloat16`` (bf16
+tensor-core math) and ``torch.float32`` ("tf32" mode: fp32 activations and weights, TF32
+tensor-core convolutions, everything else fp32 -- the precision the reference itself trains at,
+pytorch/single_gpu.py:65-72 under torch's cuDNN default).  Every op takes its type from the
+tensor it is given.
 Parameter gradients are written by the kernels straight into the parameter's
 gradient buffer (a view of the reducer's flat arena when the model is wrapped),
 so autograd never materialises or accumulates a weight gradient itself.
@@ -24,6 +29,28 @@ from .. import _native as nv
 
 # DTDL_FUSE_BN_STATS=0 keeps the separate statistics pass (A/B measurements)
 FUSE_BN_STATS = os.environ.get("DTDL_FUSE_BN_STATS", "1") != "0"
+
+ACT_DTYPES = {"bf16": torch.bfloat16, "tf32": torch.float32, "fp32": torch.float32,
+              torch.bfloat16: torch.bfloat16, torch.float32: torch.float32}
+
+
+def act_dtype(spec):
+    """'bf16' | 'tf32' | torch dtype -> the activation storage dtype."""
+    try:
+        return ACT_DTYPES[spec]
+    except KeyError:
+        raise ValueError(f"unknown precision {spec!r}: use 'bf16' or 'tf32'") from None
+
+
+def act_of(t) -> int:
+    """The ``act`` argument of the C ABI for a tensor / dtype: 0 = bf16, 1 = fp32 (TF32 math)."""
+    dt = t if isinstance(t, torch.dtype) else t.dtype
+    if dt == torch.bfloat16:
+        return 0
+    if dt == torch.float32:
+        return 1
+    raise TypeError(f"activations must be bfloat16 or float32, got {dt}")
+
 
 def pad8(c: int) -> int:
     return (c + 7) // 8 * 8
@@ -147,46 +174,47 @@ def scratch(device, nbytes: int, tag: str = "") -> torch.Tensor:
 # --------------------------------------------------------------------------------------
 # layout
 # --------------------------------------------------------------------------------------
-def to_nhwc(x: torch.Tensor, Cp: int | None = None) -> torch.Tensor:
-    """NCHW (or [N,F]) fp32 -> NHWC bf16 padded.  No gradient flows to the input.
+def to_nhwc(x: torch.Tensor, Cp: int | None = None, dtype=torch.bfloat16) -> torch.Tensor:
+    """NCHW (or [N,F]) fp32 -> NHWC padded, stored as ``dtype``.  No gradient flows to the input.
 
     The result lives on the CURRENT device even when ``x`` is a (peer-accessible) tensor of
     another GPU: the kernel then reads its batch slice over NVLink, which is how the
     single-process engine folds ``scatter`` into the first layer (K-C4)."""
     dev = torch.device("cuda", torch.cuda.current_device())
+    act = act_of(dtype)
     if x.dim() == 2:
         N, C = x.shape
         Cp = Cp or pad8(C)
-        y = torch.empty((N, 1, 1, Cp), dtype=torch.bfloat16, device=dev)
-        nv.call("f32_to_bf16_pad", nv.ptr(x.contiguous().float()), nv.ptr(y), N, C, Cp, nv.stream_ptr())
+        y = torch.empty((N, 1, 1, Cp), dtype=dtype, device=dev)
+        nv.call("pad_cast", nv.ptr(x.contiguous().float()), nv.ptr(y), N, C, Cp, act, nv.stream_ptr())
         return y
     N, C, H, W = x.shape
     Cp = Cp or pad8(C)
     x = x.detach()
     if x.dtype != torch.float32 or not x.is_contiguous():
         x = x.contiguous().float()
-    y = torch.empty((N, H, W, Cp), dtype=torch.bfloat16, device=dev)
-    nv.call("nchw_to_nhwc_bf16", nv.ptr(x), nv.ptr(y), N, C, H, W, Cp, nv.stream_ptr())
+    y = torch.empty((N, H, W, Cp), dtype=dtype, device=dev)
+    nv.call("nchw_to_nhwc", nv.ptr(x), nv.ptr(y), N, C, H, W, Cp, act, nv.stream_ptr())
     return y
 
 
 class _ToF32(torch.autograd.Function):
-    """[N,1,1,Cp] bf16 -> [N,C] fp32 (e.g. logits handed to a user criterion)."""
+    """[N,1,1,Cp] activations -> [N,C] fp32 (e.g. logits handed to a user criterion)."""
 
     @staticmethod
     def forward(ctx, x, C):
         N, Cp = x.shape[0], x.shape[-1]
-        ctx.meta = (N, C, Cp)
+        ctx.meta = (N, C, Cp, x.dtype)
         y = torch.empty((N, C), dtype=torch.float32, device=x.device)
-        nv.call("bf16_to_f32_unpad", nv.ptr(x), nv.ptr(y), N, C, Cp, nv.stream_ptr())
+        nv.call("unpad_cast", nv.ptr(x), nv.ptr(y), N, C, Cp, act_of(x), nv.stream_ptr())
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        N, C, Cp = ctx.meta
+        N, C, Cp, dtype = ctx.meta
         dy = dy.contiguous().float()
-        dx = torch.empty((N, 1, 1, Cp), dtype=torch.bfloat16, device=dy.device)
-        nv.call("f32_to_bf16_pad", nv.ptr(dy), nv.ptr(dx), N, C, Cp, nv.stream_ptr())
+        dx = torch.empty((N, 1, 1, Cp), dtype=dtype, device=dy.device)
+        nv.call("pad_cast", nv.ptr(dy), nv.ptr(dx), N, C, Cp, act_of(dtype), nv.stream_ptr())
         return dx, None
 
 
@@ -197,21 +225,23 @@ def to_f32(x, C):
 # --------------------------------------------------------------------------------------
 # convolution / linear
 # --------------------------------------------------------------------------------------
-def _conv_out(n, k, pad):
-    return n + 2 * pad - k + 1
+def _conv_out(n, k, pad, stride=1):
+    return (n + 2 * pad - k) // stride + 1
 
 
 def conv_fprop_raw(x, wpack, Cout_p, KH, KW, pad, bias=None, relu=False, out_f32=False, out_hw=None,
-                   stats=0):
+                   stats=0, stride=1):
     """``stats``: device address of a zeroed fp32 [2*Cout_p] buffer that receives the per-channel
-    sum / sum of squares of the output (the following BatchNorm's batch statistics)."""
+    sum / sum of squares of the output (the following BatchNorm's batch statistics).  The output
+    has the storage type of ``x`` (bf16 inputs may ask for an fp32 output with ``out_f32``)."""
     N, H, W, Cin_p = x.shape
-    Ho, Wo = out_hw or (_conv_out(H, KH, pad), _conv_out(W, KW, pad))
-    y = torch.empty((N, Ho, Wo, Cout_p), dtype=torch.float32 if out_f32 else torch.bfloat16,
+    Ho, Wo = out_hw or (_conv_out(H, KH, pad, stride), _conv_out(W, KW, pad, stride))
+    act = act_of(x)
+    y = torch.empty((N, Ho, Wo, Cout_p), dtype=torch.float32 if (out_f32 or act) else torch.bfloat16,
                     device=x.device)
     flags = (1 if relu else 0) | (2 if out_f32 else 0)
     nv.call("conv_fprop_stats", nv.ptr(x), nv.ptr(wpack), nv.ptr(y), nv.ptr(bias), stats, N, H, W,
-            Cin_p, Ho, Wo, Cout_p, KH, KW, pad, pad, flags, nv.stream_ptr())
+            Cin_p, Ho, Wo, Cout_p, KH, KW, pad, pad, flags, stride, act, nv.stream_ptr())
     return y
 
 
@@ -227,40 +257,40 @@ def _claim_bn_stats(bn, device, Cp):
 
 
 def subsample2_raw(x, adjoint=False, full_hw=None):
+    act = act_of(x)
     if not adjoint:
         N, H, W, Cp = x.shape
         y = torch.empty((N, (H + 1) // 2, (W + 1) // 2, Cp), dtype=x.dtype, device=x.device)
-        nv.call("subsample2", nv.ptr(x), nv.ptr(y), N, H, W, Cp, 0, nv.stream_ptr())
+        nv.call("subsample2", nv.ptr(x), nv.ptr(y), N, H, W, Cp, 0, act, nv.stream_ptr())
         return y
     N, _, _, Cp = x.shape
     H, W = full_hw
     y = torch.empty((N, H, W, Cp), dtype=x.dtype, device=x.device)
-    nv.call("subsample2", nv.ptr(x), nv.ptr(y), N, H, W, Cp, 1, nv.stream_ptr())
+    nv.call("subsample2", nv.ptr(x), nv.ptr(y), N, H, W, Cp, 1, act, nv.stream_ptr())
     return y
 
 
-class _Conv(torch.autograd.Function):
-    """Convolution (stride 1 or 2) / Linear with optional fused bias + ReLU epilogue.
+# fp32 mode: Linear layers up to this many weights run in full fp32 on CUDA cores, like the
+# reference's nn.Linear (torch keeps TF32 off for matmuls); larger ones use the TF32 tensor-core path
+LINEAR_F32_MAX_WEIGHTS = 1 << 16
 
-    Stride 2 is the stride-1 kernel followed by a 2x subsample (two layers of PyramidNet,
-    three of ResNet-50); its backward zero-inserts dy and reuses the stride-1 kernels.
-    """
+
+def _use_linear_f32(x, mod):
+    return (x.dtype == torch.float32 and mod.KH == 1 and mod.KW == 1 and x.shape[1] == 1 and x.shape[2] == 1
+            and mod.conv_stride == 1 and mod.Cout * mod.Cin <= LINEAR_F32_MAX_WEIGHTS)
+
+
+class _LinearF32(torch.autograd.Function):
+    """Small fully connected layer in full fp32 (fp32 activation mode; see LINEAR_F32_MAX_WEIGHTS)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, mod, stats_for=None):
+    def forward(ctx, x, weight, bias, mod):
         x = x.contiguous()
-        stats = 0
-        if (stats_for is not None and mod.conv_stride == 1 and FUSE_BN_STATS
-                and (stats_for.training or stats_for.running_mean is None)):
-            stats = _claim_bn_stats(stats_for, x.device, mod.Cout_p)
-        y = conv_fprop_raw(x, mod.wf, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad, bias=bias,
-                           relu=mod.fuse_relu, out_f32=False, out_hw=getattr(mod, "out_hw", None),
-                           stats=stats)
-        full_hw = (y.shape[1], y.shape[2])
-        if mod.conv_stride == 2:
-            y = subsample2_raw(y)
+        N, Kp = x.shape[0], x.shape[-1]
+        y = torch.empty((N, 1, 1, mod.Cout_p), dtype=torch.float32, device=x.device)
+        nv.call("linear_f32_fwd", nv.ptr(x), nv.ptr(weight), nv.ptr(bias), nv.ptr(y), N, mod.Cin, Kp,
+                mod.Cout, mod.Cout_p, 1 if mod.fuse_relu else 0, nv.stream_ptr())
         ctx.mod = mod
-        ctx.full_hw = full_hw
         ctx.has_bias = bias is not None
         ctx.save_for_backward(x, weight, bias, y if mod.fuse_relu else None)
         return y
@@ -271,25 +301,74 @@ class _Conv(torch.autograd.Function):
         x, weight, bias, y = ctx.saved_tensors
         dy = dy.contiguous()
         st = nv.stream_ptr()
+        N, Kp = x.shape[0], x.shape[-1]
         if mod.fuse_relu:
             g = torch.empty_like(dy)
-            nv.call("relu_bwd", nv.ptr(dy), nv.ptr(y), nv.ptr(g), dy.numel(), st)
+            nv.call("relu_bwd", nv.ptr(dy), nv.ptr(y), nv.ptr(g), dy.numel(), 1, st)
+            dy = g
+        if ctx.has_bias:
+            gb, acc = grad_buffer(bias)
+            if not acc:
+                gb.zero_()
+            nv.call("colsum", nv.ptr(dy), nv.ptr(gb), N, mod.Cout, mod.Cout_p, 1, st)
+            _grad_ready(bias)
+        gw, acc = grad_buffer(weight)
+        dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
+        nv.call("linear_f32_bwd", nv.ptr(dy), nv.ptr(x), nv.ptr(weight), nv.ptr(dx), nv.ptr(gw), N, mod.Cin,
+                Kp, mod.Cout, mod.Cout_p, acc, st)
+        _grad_ready(weight)
+        return dx, None, None, None
+
+
+class _Conv(torch.autograd.Function):
+    """Convolution (stride 1 or 2) / Linear with optional fused bias + ReLU epilogue.
+
+    Stride 2 is native: the forward and weight-gradient kernels sample the input through TMA
+    element strides, the data gradient runs in gather form over the four output phases
+    (``conv_dgrad_s2``), so a stride-2 layer does 1x the arithmetic of its definition.
+    """
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, mod, stats_for=None):
+        x = x.contiguous()
+        stats = 0
+        if (stats_for is not None and FUSE_BN_STATS
+                and (stats_for.training or stats_for.running_mean is None)):
+            stats = _claim_bn_stats(stats_for, x.device, mod.Cout_p)
+        y = conv_fprop_raw(x, mod.wf, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad, bias=bias,
+                           relu=mod.fuse_relu, out_f32=False, out_hw=getattr(mod, "out_hw", None),
+                           stats=stats, stride=mod.conv_stride)
+        ctx.mod = mod
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(x, weight, bias, y if mod.fuse_relu else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        mod = ctx.mod
+        x, weight, bias, y = ctx.saved_tensors
+        dy = dy.contiguous()
+        st = nv.stream_ptr()
+        act = act_of(x)
+        stride = mod.conv_stride
+        if mod.fuse_relu:
+            g = torch.empty_like(dy)
+            nv.call("relu_bwd", nv.ptr(dy), nv.ptr(y), nv.ptr(g), dy.numel(), act, st)
             dy = g
         if ctx.has_bias:
             gb, acc = grad_buffer(bias)
             if not acc:
                 gb.zero_()
             P = dy.shape[0] * dy.shape[1] * dy.shape[2]
-            nv.call("colsum", nv.ptr(dy), nv.ptr(gb), P, mod.Cout, mod.Cout_p, st)
+            nv.call("colsum", nv.ptr(dy), nv.ptr(gb), P, mod.Cout, mod.Cout_p, act, st)
             _grad_ready(bias)
-        if mod.conv_stride == 2:
-            dy = subsample2_raw(dy, adjoint=True, full_hw=ctx.full_hw)
         N, H, W, Cin_p = x.shape
-        Ho, Wo = ctx.full_hw
+        Ho, Wo = dy.shape[1], dy.shape[2]
         # weight gradient: straight into the parameter's gradient buffer, or -- when the weight
         # is a computed tensor (ResNet stem's space-to-depth view) -- returned to autograd
         returned = getattr(mod, "return_wgrad", False)
-        need = nv.lib().dtdl_conv_wgrad_workspace_bytes(N, Ho, Wo, Cin_p, mod.Cout_p, mod.KH, mod.KW)
+        need = nv.lib().dtdl_conv_wgrad_workspace_bytes_ex(N, Ho, Wo, Cin_p, mod.Cout_p, mod.KH, mod.KW,
+                                                           stride, act)
         side = None if returned else wgrad_stream(x.device)
         if side is not None:
             # x and dy are read on the side stream: keep the allocator from recycling them early
@@ -300,7 +379,7 @@ class _Conv(torch.autograd.Function):
                 ws = scratch(x.device, need, "side")
                 nv.call("conv_wgrad", nv.ptr(x), nv.ptr(dy), nv.ptr(gw), nv.ptr(ws), ws.numel(), N, H, W,
                         mod.Cin, Cin_p, Ho, Wo, mod.Cout, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad,
-                        mod.conv_pad, acc, side.cuda_stream)
+                        mod.conv_pad, acc, stride, act, side.cuda_stream)
                 _grad_ready(weight)
         else:
             if returned:
@@ -309,19 +388,27 @@ class _Conv(torch.autograd.Function):
                 gw, acc = grad_buffer(weight)
             ws = scratch(x.device, need)
             nv.call("conv_wgrad", nv.ptr(x), nv.ptr(dy), nv.ptr(gw), nv.ptr(ws), ws.numel(), N, H, W,
-                    mod.Cin, Cin_p, Ho, Wo, mod.Cout, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad, mod.conv_pad, acc, st)
+                    mod.Cin, Cin_p, Ho, Wo, mod.Cout, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad, mod.conv_pad,
+                    acc, stride, act, st)
             if not returned:
                 _grad_ready(weight)
         # data gradient
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = conv_fprop_raw(dy, mod.wd, Cin_p, mod.KH, mod.KW, mod.KH - 1 - mod.conv_pad)
+            if stride == 1:
+                dx = conv_fprop_raw(dy, mod.wd, Cin_p, mod.KH, mod.KW, mod.KH - 1 - mod.conv_pad)
+            else:
+                dx = torch.empty_like(x)
+                nv.call("conv_dgrad_s2", nv.ptr(dy), nv.ptr(mod.wd), nv.ptr(dx), N, Ho, Wo, mod.Cout_p, H, W,
+                        Cin_p, mod.KH, mod.KW, mod.conv_pad, mod.conv_pad, act, st)
         return dx, (gw if returned else None), None, None, None
 
 
 def conv(x, mod, stats_for=None):
     """``stats_for``: the training-mode BatchNorm2d that consumes this convolution's output; its
-    batch statistics then come out of the GEMM epilogue (stride-1 convolutions only)."""
+    batch statistics then come out of the GEMM epilogue."""
+    if _use_linear_f32(x, mod):
+        return _LinearF32.apply(x, mod.weight, mod.bias, mod)
     return _Conv.apply(x, mod.weight, mod.bias, mod, stats_for)
 
 
@@ -343,16 +430,16 @@ def subsample2(x):
     return _Subsample.apply(x)
 
 
-def to_s2d(x: torch.Tensor) -> torch.Tensor:
-    """NCHW fp32 -> 2x2 space-to-depth NHWC bf16 [N,H/2,W/2,pad8(4C)] (ResNet stem input)."""
+def to_s2d(x: torch.Tensor, dtype=torch.bfloat16) -> torch.Tensor:
+    """NCHW fp32 -> 2x2 space-to-depth NHWC [N,H/2,W/2,pad8(4C)] (ResNet stem input)."""
     N, C, H, W = x.shape
     Cp = pad8(4 * C)
     x = x.detach()
     if x.dtype != torch.float32 or not x.is_contiguous():
         x = x.contiguous().float()
-    y = torch.empty((N, H // 2, W // 2, Cp), dtype=torch.bfloat16,
+    y = torch.empty((N, H // 2, W // 2, Cp), dtype=dtype,
                     device=torch.device("cuda", torch.cuda.current_device()))
-    nv.call("nchw_to_s2d_bf16", nv.ptr(x), nv.ptr(y), N, C, H, W, Cp, nv.stream_ptr())
+    nv.call("nchw_to_s2d", nv.ptr(x), nv.ptr(y), N, C, H, W, Cp, act_of(dtype), nv.stream_ptr())
     return y
 
 
@@ -378,7 +465,7 @@ class _BatchNorm(torch.autograd.Function):
         elif training:
             if mod._fwd_dirty:
                 stat[: 2 * Cp].zero_()
-            nv.call("bn_stats", nv.ptr(x), nv.ptr(stat), P, Cp, st)
+            nv.call("bn_stats", nv.ptr(x), nv.ptr(stat), P, Cp, act_of(x), st)
             mod._fwd_dirty = True
         save = torch.empty((2, Cp), dtype=torch.float32, device=x.device)
         mom = mod.momentum if mod.momentum is not None else 0.1
@@ -392,7 +479,7 @@ class _BatchNorm(torch.autograd.Function):
                 nv.ptr(mod.num_batches_tracked) if (track and training) else 0,
                 nv.ptr(save[0]), nv.ptr(save[1]), nv.ptr(residual), Cres_p, P, C, Cp, mod.eps, mom,
                 1 if relu else 0, 1 if training else 0,
-                stat[2 * Cp:].data_ptr() if training else 0, 2 * Cp, out_sums, st)
+                stat[2 * Cp:].data_ptr() if training else 0, 2 * Cp, out_sums, act_of(x), st)
         ctx.mod, ctx.relu, ctx.Cres_p, ctx.training = mod, relu, Cres_p, training
         ctx.save_for_backward(x, y if relu else None, gamma, beta, save)
         if fork_input:
@@ -420,11 +507,11 @@ class _BatchNorm(torch.autograd.Function):
         dx = torch.empty_like(x)
         dres = None
         if ctx.Cres_p and ctx.needs_input_grad[3]:
-            dres = torch.empty((N, H, W, ctx.Cres_p), dtype=torch.bfloat16, device=x.device)
+            dres = torch.empty((N, H, W, ctx.Cres_p), dtype=x.dtype, device=x.device)
         nv.call("bn_bwd_add", nv.ptr(dy), nv.ptr(x), nv.ptr(y), nv.ptr(save[0]), nv.ptr(save[1]),
                 nv.ptr(gamma), stat[2 * Cp:].data_ptr(), nv.ptr(dx), nv.ptr(dres), ctx.Cres_p,
                 nv.ptr(gg), nv.ptr(gb), 1 if (acc_g or acc_b) else 0, P, mod.num_features, Cp,
-                1 if ctx.relu else 0, nv.ptr(stat), 2 * Cp, nv.ptr(add_in), st)
+                1 if ctx.relu else 0, nv.ptr(stat), 2 * Cp, nv.ptr(add_in), act_of(x), st)
         mod._fwd_dirty = False
         _grad_ready(gamma)
         _grad_ready(beta)
@@ -456,7 +543,7 @@ class _Pool(torch.autograd.Function):
 
         Ho, Wo = osz(H), osz(W)
         y = torch.empty((N, Ho, Wo, Cp), dtype=x.dtype, device=x.device)
-        nv.call("pool_fwd", nv.ptr(x), nv.ptr(y), N, H, W, Ho, Wo, Cp, k, stride, pad, mode,
+        nv.call("pool_fwd", nv.ptr(x), nv.ptr(y), N, H, W, Ho, Wo, Cp, k, stride, pad, mode, act_of(x),
                 nv.stream_ptr())
         ctx.meta = (k, stride, pad, mode)
         ctx.save_for_backward(x, y)
@@ -470,7 +557,7 @@ class _Pool(torch.autograd.Function):
         N, H, W, Cp = x.shape
         dx = torch.empty_like(x)
         nv.call("pool_bwd", nv.ptr(dy), nv.ptr(x), nv.ptr(y), nv.ptr(dx), N, H, W, y.shape[1],
-                y.shape[2], Cp, k, stride, pad, mode, nv.stream_ptr())
+                y.shape[2], Cp, k, stride, pad, mode, act_of(x), nv.stream_ptr())
         return dx, None, None, None, None, None
 
 
@@ -488,7 +575,7 @@ class _GlobalAvgPool(torch.autograd.Function):
         x = x.contiguous()
         N, H, W, Cp = x.shape
         y = torch.empty((N, 1, 1, Cp), dtype=x.dtype, device=x.device)
-        nv.call("gap_fwd", nv.ptr(x), nv.ptr(y), N, H * W, Cp, nv.stream_ptr())
+        nv.call("gap_fwd", nv.ptr(x), nv.ptr(y), N, H * W, Cp, act_of(x), nv.stream_ptr())
         ctx.shape = (N, H, W, Cp)
         return y
 
@@ -497,7 +584,7 @@ class _GlobalAvgPool(torch.autograd.Function):
         N, H, W, Cp = ctx.shape
         dy = dy.contiguous()
         dx = torch.empty((N, H, W, Cp), dtype=dy.dtype, device=dy.device)
-        nv.call("gap_bwd", nv.ptr(dy), nv.ptr(dx), N, H * W, Cp, nv.stream_ptr())
+        nv.call("gap_bwd", nv.ptr(dy), nv.ptr(dx), N, H * W, Cp, act_of(dy), nv.stream_ptr())
         return dx
 
 

@@ -3,7 +3,8 @@
 They subclass the torch modules of the same name, so parameter / buffer names, shapes,
 initialisation and ``state_dict`` layout are exactly torch's (the reference checkpoints
 ``model.state_dict()``: pytorch/single_gpu.py:81-84).  On CUDA tensors ``forward`` runs the
-hand-written kernels on NHWC bf16 activations; on CPU tensors it runs the stock fp32 torch op
+hand-written kernels on NHWC activations (bf16, or fp32 with TF32 tensor-core math after
+``set_precision(model, "tf32")``); on CPU tensors it runs the stock fp32 torch op
 (NCHW), which is also the numerical oracle of the test-suite.  There is no PyTorch fallback
 on a GPU: a missing native library raises.
 """
@@ -28,7 +29,9 @@ def is_native(x: torch.Tensor) -> bool:
 # weight packing (fp32 master -> bf16 tcgen05 operand layouts)
 # --------------------------------------------------------------------------------------
 class _PackedWeightMixin:
-    """Owns the bf16 fprop / dgrad packs of a conv / linear weight."""
+    """Owns the fprop / dgrad operand packs of a conv / linear weight (bf16, or fp32 in tf32 mode)."""
+
+    act_dtype = torch.bfloat16      # storage type of the packs = of the activations this layer sees
 
     def _init_pack_meta(self, Cout, Cin, KH, KW, pad, stride, need_dgrad=True):
         self.Cout, self.Cin, self.KH, self.KW = Cout, Cin, KH, KW
@@ -43,13 +46,21 @@ class _PackedWeightMixin:
 
     def _alloc_packs(self, device):
         taps = self.KH * self.KW
-        self.wf = torch.zeros(pad16(self.Cout_p) * taps * self.Cin_p, dtype=torch.bfloat16, device=device)
-        self.wd = (torch.zeros(pad16(self.Cin_p) * taps * self.Cout_p, dtype=torch.bfloat16, device=device)
+        self.wf = torch.zeros(pad16(self.Cout_p) * taps * self.Cin_p, dtype=self.act_dtype, device=device)
+        self.wd = (torch.zeros(pad16(self.Cin_p) * taps * self.Cout_p, dtype=self.act_dtype, device=device)
                    if self.need_dgrad else None)
 
-    def _ensure_packed(self):
+    def _packs_stale(self):
         w = self.weight
-        if self.wf is None or self.wf.device != w.device:
+        return self.wf is None or self.wf.device != w.device or self.wf.dtype != self.act_dtype
+
+    def _ensure_packed(self, dtype=None):
+        """``dtype``: storage type of the activation about to be multiplied (a layer called with a
+        type other than the model's configured one simply re-packs for it)."""
+        w = self.weight
+        if dtype is not None and dtype != self.act_dtype:
+            self.act_dtype = dtype
+        if self._packs_stale():
             self._alloc_packs(w.device)
             self._packed_version = None
         if self._packed_version != w._version or self._packed_ptr != w.data_ptr():
@@ -68,13 +79,13 @@ def pack_weights(modules, table_cache=None):
         host = (ctypes.c_char * (esz * len(modules)))()
         blocks = 0
         for i, m in enumerate(modules):
-            if m.wf is None or m.wf.device != m.weight.device:
+            if m._packs_stale():
                 m._alloc_packs(m.weight.device)
             entry = ctypes.addressof(host) + i * esz
             src = getattr(m, "pack_src", None)
             blocks += nv.lib().dtdl_pack_entry_fill(
                 entry, nv.ptr(src if src is not None else m.weight), nv.ptr(m.wf), nv.ptr(m.wd), m.Cout, m.Cin, m.KH * m.KW,
-                m.Cin_p, m.Cout_p, blocks)
+                m.Cin_p, m.Cout_p, blocks, fn.act_of(m.wf))
         dev = modules[0].weight.device
         table = torch.frombuffer(bytearray(bytes(host)), dtype=torch.uint8).to(dev)
         n = len(modules)
@@ -112,7 +123,7 @@ class Conv2d(nn.Conv2d, _PackedWeightMixin):
         if not is_native(x):
             y = super().forward(x)
             return F.relu(y) if self.fuse_relu else y
-        self._ensure_packed()
+        self._ensure_packed(x.dtype)
         if self.pre_subsample:
             x = fn.subsample2(x)
         return fn.conv(x, self, stats_for=stats_for)
@@ -130,7 +141,7 @@ class Linear(nn.Linear, _PackedWeightMixin):
         if not is_native(x):
             y = super().forward(x)
             return F.relu(y) if self.fuse_relu else y
-        self._ensure_packed()
+        self._ensure_packed(x.dtype)
         return fn.conv(x, self)
 
 
@@ -202,12 +213,15 @@ class GlobalAvgPool2d(nn.Module):
 
 
 class InputLayout(nn.Module):
-    """Entry of a model: NCHW / [N,F] fp32 -> the framework's NHWC bf16 layout (GPU only)."""
+    """Entry of a model: NCHW / [N,F] fp32 -> the framework's NHWC layout (GPU only), stored as
+    ``act_dtype`` (bf16 by default; ``set_precision(model, "tf32")`` switches to fp32)."""
+
+    act_dtype = torch.bfloat16
 
     def forward(self, x):
         if not is_native(x):
             return x
-        return fn.to_nhwc(x)
+        return fn.to_nhwc(x, dtype=self.act_dtype)
 
 
 class Flatten(nn.Module):
@@ -242,6 +256,27 @@ class OutputLayout(nn.Module):
         if getattr(self, "_bypass", False):
             return x  # the single-process engine converts while gathering to GPU 0
         return fn.to_f32(x, self.features)
+
+
+def set_precision(model: nn.Module, precision="bf16"):
+    """Selects the activation / operand storage type of every layer of ``model``:
+
+    * ``"bf16"`` (default): bf16 activations and weight operands, fp32 accumulation, statistics and
+      master weights -- the fastest mode;
+    * ``"tf32"``: fp32 activations and weight operands, TF32 tensor-core convolutions, fp32
+      everything else -- numerically what the reference's fp32 model does under torch's cuDNN default
+      (pytorch/single_gpu.py:65-72).
+
+    Returns the model.  Packs are rebuilt lazily at the next forward."""
+    dt = fn.act_dtype(precision)
+    for m in model.modules():
+        if isinstance(m, (_PackedWeightMixin, InputLayout)) or hasattr(m, "act_dtype"):
+            m.act_dtype = dt
+        op = getattr(m, "_op", None)        # packed-weight holders that are not modules (ResNet stem)
+        if isinstance(op, _PackedWeightMixin):
+            op.act_dtype = dt
+    model._dtdl_precision = "tf32" if dt == torch.float32 else "bf16"
+    return model
 
 
 def packed_layers(model: nn.Module):

@@ -49,11 +49,11 @@ class _GatherLogits(torch.autograd.Function):
             n, Cp = x.shape[0], x.shape[-1]
             with torch.cuda.device(x.device):
                 st = torch.cuda.current_stream(x.device)
-                nv.call("bf16_to_f32_unpad", nv.ptr(x), out[row: row + n].data_ptr(), n, C, Cp, st.cuda_stream)
+                nv.call("unpad_cast", nv.ptr(x), out[row: row + n].data_ptr(), n, C, Cp, fn.act_of(x), st.cuda_stream)
                 ev = torch.cuda.Event()
                 ev.record(st)
             main.wait_event(ev)
-            meta.append((x.device, row, n, Cp))
+            meta.append((x.device, row, n, Cp, x.dtype))
             row += n
         ctx.meta, ctx.C = meta, C
         return out
@@ -64,12 +64,12 @@ class _GatherLogits(torch.autograd.Function):
         ev0 = torch.cuda.Event()
         ev0.record(torch.cuda.current_stream(dy.device))
         grads = []
-        for dev, row, n, Cp in ctx.meta:
+        for dev, row, n, Cp, dtype in ctx.meta:
             with torch.cuda.device(dev):
                 st = torch.cuda.current_stream(dev)
                 st.wait_event(ev0)
-                dx = torch.empty((n, 1, 1, Cp), dtype=torch.bfloat16, device=dev)
-                nv.call("f32_to_bf16_pad", dy[row: row + n].data_ptr(), nv.ptr(dx), n, ctx.C, Cp, st.cuda_stream)
+                dx = torch.empty((n, 1, 1, Cp), dtype=dtype, device=dev)
+                nv.call("pad_cast", dy[row: row + n].data_ptr(), nv.ptr(dx), n, ctx.C, Cp, fn.act_of(dtype), st.cuda_stream)
             grads.append(dx)
         return (None, None) + tuple(grads)
 

@@ -261,8 +261,11 @@ class Reducer:
 
 class DistributedModel(nn.Module):
     def __init__(self, module, comm=None, optimizer=None, bucket_cap_mb=25.0, first_bucket_mb=1.0,
-                 broadcast_buffers=True, device_ids=None, output_device=None):
+                 broadcast_buffers=True, device_ids=None, output_device=None, dtype=None):
         super().__init__()
+        if dtype is not None:
+            from ..ops.modules import set_precision
+            set_precision(module, dtype)
         comm = comm or rendezvous.current() or rendezvous.init()
         self.module = module
         self.comm = comm
@@ -296,7 +299,10 @@ class DistributedModel(nn.Module):
 
 
 def wrap(model, optimizer=None, comm=None, **kw) -> DistributedModel:
-    """``net = wrap(net)`` replaces ``DistributedDataParallel(net, device_ids=[gpu])``."""
+    """``net = wrap(net)`` replaces ``DistributedDataParallel(net, device_ids=[gpu])``.
+
+    ``dtype="bf16"`` (default of the layers) or ``dtype="tf32"``: the activation / operand precision
+    of the wrapped model's layers, see ``ops.set_precision``."""
     return DistributedModel(model, comm=comm, optimizer=optimizer, **kw)
 
 

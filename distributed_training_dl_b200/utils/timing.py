@@ -73,6 +73,7 @@ class ClockSampler:
         self.samples, self.reasons, self.max_mhz = [], set(), None
         self._stop = threading.Event()
         self._thread = self._proc = None
+        self._nvml = None
 
     def _physical_index(self):
         vis = os.environ.get("CUDA_VISIBLE_DEVICES")
@@ -83,20 +84,32 @@ class ClockSampler:
                 pass
         return self.gpu_index
 
+    def _nvml_sample(self, handle, nvml):
+        self.samples.append(float(nvml.nvmlDeviceGetClockInfo(handle, nvml.NVML_CLOCK_SM)))
+        try:
+            mask = nvml.nvmlDeviceGetCurrentClocksEventReasons(handle)
+        except Exception:  # noqa: BLE001  (older bindings spell it ThrottleReasons)
+            mask = nvml.nvmlDeviceGetCurrentClocksThrottleReasons(handle)
+        for bit, name in self.REASON_BITS.items():
+            if mask & bit:
+                self.reasons.add(name)
+
     def _nvml_loop(self, handle, nvml):
         while not self._stop.is_set():
             try:
-                self.samples.append(float(nvml.nvmlDeviceGetClockInfo(handle, nvml.NVML_CLOCK_SM)))
-                try:
-                    mask = nvml.nvmlDeviceGetCurrentClocksEventReasons(handle)
-                except Exception:  # noqa: BLE001  (older bindings spell it ThrottleReasons)
-                    mask = nvml.nvmlDeviceGetCurrentClocksThrottleReasons(handle)
-                for bit, name in self.REASON_BITS.items():
-                    if mask & bit:
-                        self.reasons.add(name)
+                self._nvml_sample(handle, nvml)
             except Exception:  # noqa: BLE001
                 break
             self._stop.wait(self.period_ms / 1e3)
+
+    def sample_now(self):
+        """One synchronous sample from the calling thread (the timed loop calls this while the GPU is
+        busy, so a region too short for the background thread still has a clock record)."""
+        if self._nvml is not None:
+            try:
+                self._nvml_sample(*self._nvml)
+            except Exception:  # noqa: BLE001
+                pass
 
     def __enter__(self):
         try:
@@ -104,6 +117,7 @@ class ClockSampler:
             nvml.nvmlInit()
             handle = nvml.nvmlDeviceGetHandleByIndex(self._physical_index())
             self.max_mhz = float(nvml.nvmlDeviceGetMaxClockInfo(handle, nvml.NVML_CLOCK_SM))
+            self._nvml = (handle, nvml)
             self._thread = threading.Thread(target=self._nvml_loop, args=(handle, nvml), daemon=True)
             self._thread.start()
             return self

@@ -30,7 +30,7 @@ def _c_lib():
     lib.dtdl_conv_wgrad_workspace_bytes.argtypes = [i] * 7
     lib.dtdl_conv_wgrad_static_scratch_bytes.restype = ll
     lib.dtdl_conv_wgrad.restype = i
-    lib.dtdl_conv_wgrad.argtypes = [vp, vp, vp, vp, ll] + [i] * 14 + [vp]
+    lib.dtdl_conv_wgrad.argtypes = [vp, vp, vp, vp, ll] + [i] * 16 + [vp]   # ... accumulate, stride, act
     lib.dtdl_conv_wgrad_static.restype = i
     lib.dtdl_conv_wgrad_static.argtypes = [vp, vp, vp] + [i] * 14 + [vp]
     return lib
@@ -58,11 +58,15 @@ def test_static_scratch_wgrad_matches_workspace_wgrad():
         got = torch.full((Cout, Cin, K, K), float("nan"), device="cuda")
         ws = torch.empty(need, dtype=torch.uint8, device="cuda")     # the caller-side workspace
         rc = lib.dtdl_conv_wgrad(x.data_ptr(), dy.data_ptr(), want.data_ptr(), ws.data_ptr(), need,
-                                 *shape, stream)
+                                 *shape, 1, 0, stream)      # stride 1, bf16 operands
         assert rc == 0, lib.dtdl_last_error()
+        torch.cuda.synchronize()
+        free_before = torch.cuda.mem_get_info()[0]
         rc = lib.dtdl_conv_wgrad_static(x.data_ptr(), dy.data_ptr(), got.data_ptr(), *shape, stream)
         assert rc == 0, lib.dtdl_last_error()
         torch.cuda.synchronize()
+        if call > 0:    # the first call may still load the kernels' code; after that: no new memory
+            assert torch.cuda.mem_get_info()[0] == free_before
         assert torch.isfinite(got).all()
         assert _rel_err(got, want) < 1e-2      # the tolerance the op tests use
         # and both agree with plain PyTorch
