@@ -240,6 +240,12 @@ class Reducer:
         """Makes reduced gradients visible to the current stream (non-fused use)."""
         self.finish_step(fused=False)
 
+    def close(self):
+        """Detaches this reducer from the op layer's gradient-ready notifications (a process that
+        wraps several models one after the other calls this before dropping a wrapped model)."""
+        fn.remove_ready_hook(self._hook)
+        self._pending = None
+
     def bucket_report(self, clear=True):
         """Per-bucket time and achieved bus bandwidth of the collectives timed since the last call
         (SURVEY.md section 5.5).  Bus bandwidth = 2 (W-1)/W * bytes / time, the figure NCCL's
