@@ -510,6 +510,10 @@ extern "C" int dtdl_comm_allreduce(void* handle, void* const* grads, void* const
   DTDL_REQUIRE(!fill_peers(&a.dst, dst, h->d.world, offset_bytes), "missing peer pointer");
   a.n = n;
   a.opt = OPT_NONE;
+  // In place (grads == dst) the one-shot schedule would let a rank overwrite its bucket while peers
+  // are still reading it: in-place calls always run the two-shot schedule, where rank r reduces and
+  // rewrites only the slice it owns.
+  if (h->d.world > 1 && grads[h->d.rank] == dst[h->d.rank]) two_shot = 1;
   a.two_shot = two_shot;
   a.scale = scale;
   const int grid = comm_grid(n / 4, h->d.world, two_shot, max_blocks > 0 ? max_blocks : 64);

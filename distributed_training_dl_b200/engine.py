@@ -54,6 +54,7 @@ class TrainStep:
         self.use_graph = graph and self.device.type == "cuda"
         self.warmup = warmup
         self._slots = {}
+        self._packed = None
         self._done = None
         self._stats = None
         self.launches_per_step = None
@@ -93,6 +94,19 @@ class TrainStep:
         self.launches_per_step = nv.launch_count()
         slot.update(graph=g, loss=loss, stats=stats)
 
+    def _refresh_stale_packs(self):
+        """A captured step re-packs the operand copies of the weights at its END, so weights changed
+        from outside between two replays (load_state_dict, load_model, a manual copy_) would be
+        multiplied from stale packs in the next forward.  torch bumps a tensor's version on every
+        in-place write, which makes such a change cheap to notice; the packs are then rebuilt
+        before the replay."""
+        from .ops.modules import pack_weights, packed_layers
+        if self._packed is None:
+            self._packed = packed_layers(self.model)
+        if any(m._packed_version != m.weight._version or m._packed_ptr != m.weight.data_ptr()
+               for m in self._packed):
+            pack_weights(self._packed)
+
     def __call__(self, x, t):
         if not self.use_graph:
             if x.device != self.device:
@@ -107,15 +121,17 @@ class TrainStep:
                 return loss
             torch.cuda.synchronize(self.device)
             self._capture(slot)
+        self._refresh_stale_packs()
         opt = self.optimizer
         if hasattr(opt, "refresh_hyper"):
-            if getattr(opt, "hyper_changes_every_step", False) and self._done is not None:
-                self._done.synchronize()  # the previous replay must have read its values
-            opt.refresh_hyper(enqueue_copy=False)  # the graph re-reads the pinned block
+            # the graph re-reads the pinned block; if the values changed (Adam: every step, SGD: when a
+            # scheduler moved lr) refresh_hyper first waits for the previous replay's read of it
+            opt.refresh_hyper(enqueue_copy=False)
         slot["graph"].replay()
-        if getattr(opt, "hyper_changes_every_step", False):
+        if hasattr(opt, "guard_hyper"):
             self._done = torch.cuda.Event()
             self._done.record()
+            opt.guard_hyper(self._done)
         if hasattr(opt, "_step"):
             opt._step += 1
         self._stats = slot["stats"]

@@ -40,7 +40,8 @@ class _GatherLogits(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, C, out_device, *xs):
+    def forward(ctx, C, out_device, world, *xs):
+        ctx.world = world
         N = sum(x.shape[0] for x in xs)
         out = torch.empty((N, C), dtype=torch.float32, device=out_device)
         main = torch.cuda.current_stream(out_device)
@@ -60,7 +61,11 @@ class _GatherLogits(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
-        dy = dy.contiguous()
+        # The user's loss is a mean over the GLOBAL batch, so a replica's parameter gradient is only
+        # its shard's share of it; the bucket reduction then AVERAGES over replicas (the kernels'
+        # 1/world).  Scaling the logits' gradient by world makes that average the true gradient --
+        # the same correction DataParallelStep's shard loss applies (world / total).
+        dy = (dy * float(ctx.world)).contiguous()
         ev0 = torch.cuda.Event()
         ev0.record(torch.cuda.current_stream(dy.device))
         grads = []
@@ -71,7 +76,7 @@ class _GatherLogits(torch.autograd.Function):
                 dx = torch.empty((n, 1, 1, Cp), dtype=dtype, device=dev)
                 nv.call("pad_cast", dy[row: row + n].data_ptr(), nv.ptr(dx), n, ctx.C, Cp, fn.act_of(dtype), st.cuda_stream)
             grads.append(dx)
-        return (None, None) + tuple(grads)
+        return (None, None, None) + tuple(grads)
 
 
 class _ShardLoss(torch.autograd.Function):
@@ -149,8 +154,19 @@ class DataParallel(nn.Module):
         return self.arenas[0]
 
     def shard_bounds(self, N):
-        per = (N + self.world - 1) // self.world
-        return [(g * per, min(N, (g + 1) * per)) for g in range(self.world)]
+        """Balanced split of a batch of N over the replicas (the first N % world shards get one
+        more sample).  Every replica must own at least one sample: its collectives are part of every
+        step, and a replica without a backward pass would contribute stale gradients."""
+        if N < self.world:
+            raise ValueError(f"batch of {N} samples cannot be split over {self.world} GPUs: "
+                             "need at least one sample per replica")
+        base, rem = divmod(N, self.world)
+        bounds, lo = [], 0
+        for g in range(self.world):
+            hi = lo + base + (1 if g < rem else 0)
+            bounds.append((lo, hi))
+            lo = hi
+        return bounds
 
     def sync_buffers_on(self, g):
         """Replica 0's BatchNorm running statistics become replica g's (K-C2)."""
@@ -211,7 +227,7 @@ class DataParallel(nn.Module):
                 continue
             with torch.cuda.device(self.devices[g]):
                 outs.append(self.run_replica_body(g, x[lo:hi]))
-        return _GatherLogits.apply(self.out_features, d0, *outs)
+        return _GatherLogits.apply(self.out_features, d0, self.world, *outs)
 
     # ------------------------------------------------------------------ reducer interface (FusedSGD)
     def finish_step(self, fused=True):
@@ -332,9 +348,7 @@ class DataParallelStep:
                 self._sx = torch.empty(x.shape, dtype=torch.float32, device=self.d0)
                 self._st = torch.empty(t.shape, dtype=torch.int64, device=self.d0)
                 self._graphs, self._calls = None, 0
-            if opt.hyper_changes_every_step and self._done is not None:
-                self._done.synchronize()
-            opt.refresh_hyper(enqueue_copy=False)
+            opt.refresh_hyper(enqueue_copy=False)   # waits for the previous step's read if values changed
             self._sx.copy_(x, non_blocking=True)
             self._st.copy_(t, non_blocking=True)
             self._stats.zero_()
@@ -349,8 +363,8 @@ class DataParallelStep:
         self._run_all()
         self._join()
         opt._step += 1
-        if opt.hyper_changes_every_step:
-            self._done = torch.cuda.Event()
-            self._done.record(torch.cuda.current_stream(self.d0))
+        self._done = torch.cuda.Event()
+        self._done.record(torch.cuda.current_stream(self.d0))
+        opt.guard_hyper(self._done)
         with torch.cuda.device(self.d0):
             return self._stats.clone()

@@ -46,6 +46,7 @@ class _FusedBase(torch.optim.Optimizer):
         self._arenas = []          # one per replica this optimizer drives
         self._states = []          # per replica: {state name: flat fp32 tensor}
         self._hyper_host = None
+        self._hyper_guards = []
         self._hyper_devs = []
         self._pack_caches = []
         self._own_packed = None
@@ -122,12 +123,26 @@ class _FusedBase(torch.optim.Optimizer):
         enqueues its copy to the device(s).  A captured CUDA graph re-reads the pinned block on
         every replay, so calling this with ``enqueue_copy=False`` before a replay is enough."""
         vals = self._hyper_values(self._world())
-        self._hyper_host[: len(vals)] = torch.tensor(vals, dtype=torch.float32)
+        new = torch.tensor(vals, dtype=torch.float32)
+        if not torch.equal(self._hyper_host[: len(vals)], new):
+            # The block is about to change while an earlier step's copy of it (enqueued below, or a
+            # node of a replayed graph) may not have run yet: that step must not see the new values.
+            for ev in self._hyper_guards:
+                ev.synchronize()
+            self._hyper_host[: len(vals)] = new
+        self._hyper_guards = []
         if enqueue_copy:
             for h in self._hyper_devs:
                 if h is not None:
                     with torch.cuda.device(h.device):
                         h.copy_(self._hyper_host, non_blocking=True)
+                        ev = torch.cuda.Event()
+                        ev.record()
+                        self._hyper_guards.append(ev)
+
+    def guard_hyper(self, event):
+        """``event`` completes after a consumer of the pinned block (a graph replay) has read it."""
+        self._hyper_guards.append(event)
 
     # ------------------------------------------------------------------ step
     def zero_grad(self, set_to_none: bool = True):

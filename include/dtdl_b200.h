@@ -171,6 +171,8 @@ int dtdl_enable_peer_access(int dev, int peer);
  * -1: query failed.  The shipped collectives are the P2P variants; multicast ones are gated on this. */
 int dtdl_multicast_supported(int device);
 int dtdl_comm_barrier(void* handle, void* stream);
+/* dst[r] = scale * sum over ranks of grads[r].  two_shot 0 = one-shot (every rank reads all peers;
+ * needs dst != grads), 1 = two-shot; an in-place call (dst == grads) always runs two-shot. */
 int dtdl_comm_allreduce(void* handle, void* const* grads, void* const* dst, long long offset_bytes,
                         long long n, float scale, int two_shot, int max_blocks, void* stream);
 /* opt: 1 = SGD momentum, 2 = Adam (torch), 3 = Adam (Keras epsilon placement).

@@ -115,6 +115,74 @@ def collectives(i, world, outdir, nvls=False):
     dtdl.shutdown()
 
 
+def collectives_sweep(i, world, outdir, nvls=False):
+    """every all-reduce variant x message sizes from 1 KiB up x >= 10 repetitions,
+    result == the exact sum on every rank.  Inputs are small integers stored as fp32, so every partial
+    sum is exact whatever the order of additions: equality is BITWISE, which also shows that all ranks
+    hold identical bits, and a cross-GPU race (a rank reading a peer's buffer too early / late) shows
+    up as a wrong integer instead of hiding inside a tolerance.  DTDL_TEST_MAX_BYTES caps the sweep
+    (default 64 MiB; the 8-GPU evidence run sets 1 GiB)."""
+    import distributed_training_dl_b200 as dtdl
+    comm = _init_nvls(dtdl, outdir, i) if nvls else dtdl.init(backend="b200")
+    if comm is None:
+        return
+    peer, dev = comm.peer, comm.device
+    max_bytes = int(os.environ.get("DTDL_TEST_MAX_BYTES", 64 << 20))
+    sizes = [s for s in (1 << 10, 64 << 10, 4 << 20, 64 << 20, 1 << 30) if s <= max_bytes]
+    reps = int(os.environ.get("DTDL_TEST_REPS", "10"))
+    nmax = max(sizes) // 4
+    buf, out = peer.alloc(nmax * 4), peer.alloc(nmax * 4)
+    x, y = buf.view(torch.float32, 0, nmax), out.view(torch.float32, 0, nmax)
+    idx = torch.arange(nmax, device=dev, dtype=torch.int64)
+
+    def pattern(rank, rep, n):
+        return (((idx[:n] * 7 + rank * 13 + rep * 5) % 1024) - 512).float()
+
+    variants = [("nvls", 2)] if nvls else [("one-shot", 0), ("two-shot", 1)]
+    for name, two_shot in variants:
+        for nbytes in sizes:
+            n = nbytes // 4
+            for rep in range(reps):
+                want = sum(pattern(r, rep, n) for r in range(world))
+                x[:n].copy_(pattern(i, rep, n))
+                y[:n].fill_(-1.0)
+                peer.allreduce(buf, 0, n, scale=1.0, two_shot=two_shot, dst=out)
+                torch.cuda.synchronize()
+                assert torch.equal(y[:n], want), (name, nbytes, rep, "out of place")
+                peer.allreduce(buf, 0, n, scale=1.0, two_shot=two_shot)      # in place
+                torch.cuda.synchronize()
+                assert torch.equal(x[:n], want), (name, nbytes, rep, "in place")
+                comm.barrier()
+            if i == 0:
+                print(f"[collectives_sweep] world {world} {name:8s} {nbytes:>11d} B x {reps} reps: exact on every rank",
+                      flush=True)
+    # fused all-reduce + SGD update at every size: equal to the unfused arithmetic, identical bits on all ranks
+    for name, two_shot in ([("nvls", 2)] if nvls else [("one-shot", 0), ("two-shot", 1)]):
+        for nbytes in sizes:
+            n = nbytes // 4
+            params = peer.alloc(n * 4)
+            ms = peer.alloc(n * 4)
+            p, m = params.view(torch.float32, 0, n), ms.view(torch.float32, 0, n)
+            lr, mu, wd = 0.125, 0.5, 0.0
+            hyper = torch.tensor([lr, mu, wd, 1.0 / world, 0, 0, 0, 1, 1, 0.0] + [0.0] * 6, device=dev)
+            p0 = pattern(3, 1, n) / 64
+            p.copy_(p0)
+            m.zero_()
+            x[:n].copy_(pattern(i, 0, n) * world)             # mean over ranks stays an exact integer
+            peer.reduce_update(buf, params, m, None, hyper, 0, n, 1, two_shot=two_shot)
+            torch.cuda.synchronize()
+            gavg = sum(pattern(r, 0, n) for r in range(world))
+            want = p0 - lr * gavg
+            assert torch.equal(p, want), (name, nbytes, "fused sgd", (p - want).abs().max().item())
+            comm.barrier()
+            params.free()
+            ms.free()
+            if i == 0:
+                print(f"[collectives_sweep] world {world} fused SGD {name:8s} {nbytes:>11d} B: exact on every rank", flush=True)
+    _ok(outdir, i)
+    dtdl.shutdown()
+
+
 def ddp_training(i, world, outdir, use_graph, nvls=False):
     import distributed_training_dl_b200 as dtdl
     from distributed_training_dl_b200.engine import CrossEntropyLoss, TrainStep
@@ -212,6 +280,42 @@ def data_parallel_engine(outdir):
 
     assert replicas_identical(), "replicas diverged (eager)"
     del loss  # an autograd graph of the eager path must not be alive while graphs are captured
+    # eager call contract on a BN-free model == single-process torch SGD on the whole batch (the
+    # replicas' gradients must add up to the gradient of the GLOBAL mean loss, weight decay unscaled);
+    # an uneven batch (one sample more than a multiple of the GPU count) exercises the balanced split
+    from distributed_training_dl_b200.models import MLP
+    torch.manual_seed(4)
+    mlp_e = MLP(n_units=64)
+    ref_e = copy.deepcopy(mlp_e)
+    dpe = dtdl.DataParallel(mlp_e, device_ids=list(range(ndev)))
+    opte = dtdl.FusedSGD(dpe.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-2)
+    ropte = torch.optim.SGD(ref_e.parameters(), lr=0.05, momentum=0.9, weight_decay=1e-2)
+    ge = torch.Generator().manual_seed(12)
+    for it in range(3):
+        nb = 16 * ndev + (1 if it == 1 else 0)
+        xb = torch.randn(nb, 784, generator=ge)
+        tb = torch.randint(0, 10, (nb,), generator=ge)
+        le = F.cross_entropy(dpe(xb.cuda(0)), tb.cuda(0))
+        opte.zero_grad()
+        le.backward()
+        opte.step()
+        rl = F.cross_entropy(ref_e(xb), tb)
+        ropte.zero_grad()
+        rl.backward()
+        ropte.step()
+        assert abs(le.item() - rl.item()) < 3e-2, (le.item(), rl.item())
+    for d in range(ndev):
+        torch.cuda.synchronize(d)
+    for (n_, p), q in zip(dpe.module.named_parameters(), ref_e.parameters()):
+        err = (p.detach().cpu() - q).abs().max().item()
+        assert err < 5e-3, ("eager DataParallel vs torch SGD", n_, err)
+    del le
+    if ndev > 1:
+        try:
+            dpe(torch.randn(ndev - 1, 784, device="cuda:0"))
+            raise AssertionError("a batch smaller than the GPU count must be rejected")
+        except ValueError:
+            pass
     # graph fast path
     step = dtdl.DataParallelStep(dp, opt, graph=True, warmup=2)
     xs, ts = x.cpu().pin_memory(), t.cpu().pin_memory()
@@ -226,7 +330,6 @@ def data_parallel_engine(outdir):
     sd = opt.state_dict()
     assert "momentum_buffer" in sd["state"][0]
     # BN-free model: k graph steps == single-process fp32 SGD on the whole batch
-    from distributed_training_dl_b200.models import MLP
     torch.manual_seed(3)
     mlp = MLP(n_units=64)
     ref = copy.deepcopy(mlp)

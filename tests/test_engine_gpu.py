@@ -116,3 +116,32 @@ def test_pinned_prefetcher_feeds_async_copies():
     assert len(ptrs) <= 3
     for i, (x, t) in enumerate(batches):
         assert torch.equal(dev_x[i].cpu(), x) and torch.equal(dev_t[i].cpu(), t), i
+
+
+def test_weights_loaded_into_a_captured_step_are_used_by_the_next_replay():
+    """A captured step re-packs the weight operands at its end, so weights loaded from outside between
+    two replays used to be multiplied from the previous packs for one step.  TrainStep now notices the
+    change (tensor version) and re-packs before replaying: a step after load_state_dict(zeros for the
+    last layer) must produce exactly uniform logits, i.e. loss == log(10)."""
+    import math
+    import distributed_training_dl_b200 as dtdl
+    from distributed_training_dl_b200.engine import CrossEntropyLoss, TrainStep
+    from distributed_training_dl_b200.models import MnistCNN
+    torch.manual_seed(0)
+    net = dtdl.wrap(MnistCNN().cuda())
+    opt = dtdl.FusedSGD(net.parameters(), lr=0.0, momentum=0.0)
+    step = TrainStep(net, opt, CrossEntropyLoss(), graph=True, warmup=1)
+    x = torch.randn(32, 1, 28, 28).pin_memory()
+    t = torch.randint(0, 10, (32,)).pin_memory()
+    for _ in range(4):
+        before = step(x, t).item()
+    assert step.launches_per_step, "graph not captured"
+    assert abs(before - math.log(10)) > 1e-3
+    sd = net.state_dict()
+    last_w = [k for k in sd if k.endswith("weight")][-1]
+    last_b = last_w[:-6] + "bias"
+    sd[last_w] = torch.zeros_like(sd[last_w])
+    sd[last_b] = torch.zeros_like(sd[last_b])
+    net.load_state_dict(sd)
+    after = step(x, t).item()          # a replay; lr = 0, so nothing else changes
+    assert abs(after - math.log(10)) < 1e-4, (before, after)
