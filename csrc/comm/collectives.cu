@@ -6,6 +6,8 @@
 // with ordinary ld/st; ordering between ranks uses system-scope release /
 // acquire on per-rank flag words with a monotonically increasing epoch that
 // lives in device memory, so the same launch can be replayed from a CUDA graph.
+// The flag exchanges are one-CTA kernels in front of / behind the data kernels
+// (sync_kernel below), so a data kernel never spins on a peer.
 //
 //   one-shot : every rank reads all W copies of the whole bucket and reduces
 //              locally (latency optimal, W x read traffic; small buckets)
@@ -39,17 +41,42 @@ namespace dtdl {
 
 static constexpr int kMaxWorld = 16;
 
+// Cross-GPU synchronisation is done by one-CTA kernels of its own (sync_kernel), not inside the data
+// kernels: a data kernel of up to 64 CTAs x 512 threads that spins on peer flags holds SM slots that
+// the backward pass running next to it wants, for as long as the slowest rank is late.  With the
+// wait in a 32-thread kernel in front of it, the data kernel starts only when every rank is ready and
+// never spins.  Two flag rows with one epoch word each:
+//   START : "everything I enqueued before this collective is complete" -- exchanged before the data
+//           kernel reads peer buffers (each bucket);
+//   DONE  : "my data kernels have finished reading / writing your buffers" -- exchanged before the
+//           buffers are touched again.  In a training step only ONE such exchange is needed, after the
+//           last bucket (the buckets touch disjoint memory, and bucket k+1's START already implies
+//           that every rank has finished bucket k): dtdl_comm_defer_done switches the per-collective
+//           DONE off and the caller closes the step with dtdl_comm_barrier.
+// Epochs live in device memory and only ever grow, so the same launches can be replayed from a graph.
 struct CommDev {
   int rank, world;
   uint32_t* flags_local;           // [2][kMaxWorld]: START row, DONE row
   uint32_t* flags_peer[kMaxWorld]; // peers' flags_local
-  uint32_t* epoch;                 // device word, last completed epoch
-  uint32_t* counter;               // device word, finished-block ticket
+  uint32_t* epochs;                // device words [2]: last completed epoch of each row
 };
+
+// Timeline of the collectives of one step, written by the kernels themselves so that it also works
+// inside a replayed graph: slot = {first block's start, last block's end (globaltimer ns), kind,
+// bytes}.  Slots are handed out in launch order from dtdl_comm_trace(); a captured launch keeps the
+// slot it got at capture time.
+struct TraceSlot {
+  unsigned long long t0, t1, kind, bytes;
+};
+enum { TR_START = 1, TR_DONE = 2, TR_REDUCE = 3, TR_NVLS_REDUCE = 4, TR_BROADCAST = 5, TR_ALLGATHER = 6,
+       TR_MARK = 7, TR_LOCAL_UPDATE = 8 };
 
 struct CommHost {
   CommDev d;
   int device;
+  int defer_done;
+  TraceSlot* trace;
+  int trace_cap, trace_next;
 };
 
 struct PeerPtrs {
@@ -63,54 +90,58 @@ enum { H_LR = 0, H_MOM, H_WD, H_INVW, H_B1, H_B2, H_EPS, H_BC1, H_BC2S, H_DAMP }
 
 enum { OPT_NONE = 0, OPT_SGD = 1, OPT_ADAM = 2, OPT_ADAM_KERAS = 3 };
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void trace_enter(TraceSlot* s, int kind, long long bytes) {
+  if (s != nullptr && blockIdx.x == 0 && threadIdx.x == 0) {
+    s->t0 = globaltimer_ns();
+    s->kind = (unsigned long long)kind;
+    s->bytes = (unsigned long long)bytes;
+  }
+}
+__device__ __forceinline__ void trace_exit(TraceSlot* s) {
+  if (s != nullptr && threadIdx.x == 0) atomicMax(&s->t1, globaltimer_ns());
+}
+
 __device__ __forceinline__ void spin_until_ge(const uint32_t* p, uint32_t want, int tag) {
   long long t0 = clock64();
   while ((int32_t)(ld_acquire_sys(p) - want) < 0) {
+    __nanosleep(40);
     if (clock64() - t0 > DTDL_SPIN_TIMEOUT_CYCLES) {
-      printf("[dtdl] peer flag wait timed out (tag %d): block %d thread %d want %u have %u\n", tag,
-             blockIdx.x, threadIdx.x, want, ld_relaxed_sys(p));
+      printf("[dtdl] peer flag wait timed out (row %d): thread %d want %u have %u\n", tag, threadIdx.x,
+             want, ld_relaxed_sys(p));
       __trap();
     }
   }
 }
 
-// All blocks: wait until every rank has announced epoch e on the START row.
-__device__ __forceinline__ void comm_start(const CommDev& c, uint32_t e) {
-  if (c.world == 1) return;
-  if (blockIdx.x == 0 && threadIdx.x < c.world) {
+// One CTA of 32 threads: thread r announces this rank's epoch to rank r and waits for rank r's.
+__global__ void __launch_bounds__(32)
+sync_kernel(const CommDev c, int row, TraceSlot* slot) {
+  trace_enter(slot, row == 0 ? TR_START : TR_DONE, 0);
+  const uint32_t e = c.epochs[row] + 1;
+  if (threadIdx.x < c.world) {
     __threadfence_system();
-    st_release_sys(c.flags_peer[threadIdx.x] + c.rank, e);
+    st_release_sys(c.flags_peer[threadIdx.x] + row * kMaxWorld + c.rank, e);
+    spin_until_ge(c.flags_local + row * kMaxWorld + threadIdx.x, e, row);
   }
-  if (threadIdx.x < c.world) spin_until_ge(c.flags_local + threadIdx.x, e, 1);
-  __syncthreads();
-}
-
-// All blocks: the last block to arrive announces DONE to every rank, waits for
-// every rank's DONE (so nobody still reads or writes our buffers when the
-// kernel exits) and publishes the epoch.
-__device__ __forceinline__ void comm_finish(const CommDev& c, uint32_t e) {
-  __threadfence_system();
-  __syncthreads();
-  __shared__ int is_last;
+  __syncwarp();
   if (threadIdx.x == 0) {
-    const unsigned ticket = atomicAdd(c.counter, 1u);
-    is_last = (ticket == gridDim.x - 1);
-  }
-  __syncthreads();
-  if (!is_last) return;
-  if (c.world > 1) {
-    if (threadIdx.x < c.world) {
-      __threadfence_system();
-      st_release_sys(c.flags_peer[threadIdx.x] + kMaxWorld + c.rank, e);
-      spin_until_ge(c.flags_local + kMaxWorld + threadIdx.x, e, 2);
-    }
-    __syncthreads();
-  }
-  if (threadIdx.x == 0) {
-    *c.counter = 0;
-    *c.epoch = e;
+    c.epochs[row] = e;
     __threadfence();
   }
+  trace_exit(slot);
+}
+
+__global__ void trace_mark_kernel(TraceSlot* slot, int kind) {
+  const unsigned long long t = globaltimer_ns();
+  slot->t0 = t;
+  atomicMax(&slot->t1, t);
+  slot->kind = (unsigned long long)kind;
+  slot->bytes = 0;
 }
 
 __device__ __forceinline__ float4 f4_add(float4 a, float4 b) {
@@ -203,10 +234,9 @@ __device__ __forceinline__ void reduce_finish(const CommDev& c, const ReduceArgs
 // bytes in flight per SM, not instruction count, set the achieved bandwidth.
 template <int WT>
 __global__ void __launch_bounds__(512)
-reduce_kernel(const CommDev c, const ReduceArgs a) {
+reduce_kernel(const CommDev c, const ReduceArgs a, TraceSlot* slot) {
   constexpr int kUnroll = 4;
-  const uint32_t e = *c.epoch + 1;
-  comm_start(c, e);
+  trace_enter(slot, TR_REDUCE, a.n * 4);
 
   const int W = WT ? WT : c.world;
   long long begin4 = 0, end4 = a.n / 4;
@@ -243,16 +273,17 @@ reduce_kernel(const CommDev c, const ReduceArgs a) {
       if (i < end4) reduce_finish<WT>(c, a, W, i, s[u]);
     }
   }
-  comm_finish(c, e);
+  trace_exit(slot);
 }
 
-static void launch_reduce(const CommDev& d, const ReduceArgs& a, int grid, cudaStream_t stream) {
+static void launch_reduce(const CommDev& d, const ReduceArgs& a, int grid, cudaStream_t stream,
+                          TraceSlot* slot) {
   switch (d.world) {
-    case 1: reduce_kernel<1><<<grid, 512, 0, stream>>>(d, a); break;
-    case 2: reduce_kernel<2><<<grid, 512, 0, stream>>>(d, a); break;
-    case 4: reduce_kernel<4><<<grid, 512, 0, stream>>>(d, a); break;
-    case 8: reduce_kernel<8><<<grid, 512, 0, stream>>>(d, a); break;
-    default: reduce_kernel<0><<<grid, 512, 0, stream>>>(d, a); break;
+    case 1: reduce_kernel<1><<<grid, 512, 0, stream>>>(d, a, slot); break;
+    case 2: reduce_kernel<2><<<grid, 512, 0, stream>>>(d, a, slot); break;
+    case 4: reduce_kernel<4><<<grid, 512, 0, stream>>>(d, a, slot); break;
+    case 8: reduce_kernel<8><<<grid, 512, 0, stream>>>(d, a, slot); break;
+    default: reduce_kernel<0><<<grid, 512, 0, stream>>>(d, a, slot); break;
   }
 }
 
@@ -276,10 +307,9 @@ __device__ __forceinline__ void multimem_st_f4(float* mc, float4 v) {
 // in which the switch adds the W values is fixed by the hardware, not by rank; results are
 // still identical on every rank because every rank receives the same stored value.
 __global__ void __launch_bounds__(512)
-nvls_reduce_kernel(const CommDev c, const ReduceArgs a) {
+nvls_reduce_kernel(const CommDev c, const ReduceArgs a, TraceSlot* slot) {
   constexpr int kUnroll = 4;
-  const uint32_t e = *c.epoch + 1;
-  comm_start(c, e);
+  trace_enter(slot, TR_REDUCE, a.n * 4);
   const int W = c.world;
   const long long n4 = a.n / 4;
   const long long per = (n4 + W - 1) / W;
@@ -301,27 +331,26 @@ nvls_reduce_kernel(const CommDev c, const ReduceArgs a) {
       if (i < end4) multimem_st_f4(a.mc_dst + 4 * i, reduce_epilogue(a, i, s[u]));
     }
   }
-  comm_finish(c, e);
+  trace_exit(slot);
 }
 
 // The root pushes its copy once; the switch delivers it to every rank (the root included).
 __global__ void __launch_bounds__(512)
-nvls_broadcast_kernel(const CommDev c, const float* local, float* mc, long long n16, int root) {
-  const uint32_t e = *c.epoch + 1;
-  comm_start(c, e);
+nvls_broadcast_kernel(const CommDev c, const float* local, float* mc, long long n16, int root,
+                      TraceSlot* slot) {
+  trace_enter(slot, TR_BROADCAST, n16 * 16);
   if (c.rank == root) {
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += stride)
       multimem_st_f4(mc + 4 * i, reinterpret_cast<const float4*>(local)[i]);
   }
-  comm_finish(c, e);
+  trace_exit(slot);
 }
 
 // Every non-root rank pulls `n16` 16-byte words from the root's copy.
 __global__ void __launch_bounds__(512)
-broadcast_kernel(const CommDev c, const PeerPtrs buf, long long n16, int root) {
-  const uint32_t e = *c.epoch + 1;
-  comm_start(c, e);
+broadcast_kernel(const CommDev c, const PeerPtrs buf, long long n16, int root, TraceSlot* slot) {
+  trace_enter(slot, TR_BROADCAST, n16 * 16);
   if (c.rank != root) {
     const uint4* src = reinterpret_cast<const uint4*>(buf.p[root]);
     uint4* dst = reinterpret_cast<uint4*>(buf.p[c.rank]);
@@ -329,14 +358,13 @@ broadcast_kernel(const CommDev c, const PeerPtrs buf, long long n16, int root) {
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n16; i += stride)
       dst[i] = src[i];
   }
-  comm_finish(c, e);
+  trace_exit(slot);
 }
 
 // all-gather: rank r pushes its slice of `buf` into every peer's copy.
 __global__ void __launch_bounds__(512)
-allgather_kernel(const CommDev c, const PeerPtrs buf, long long n16) {
-  const uint32_t e = *c.epoch + 1;
-  comm_start(c, e);
+allgather_kernel(const CommDev c, const PeerPtrs buf, long long n16, TraceSlot* slot) {
+  trace_enter(slot, TR_ALLGATHER, n16 * 16);
   const int W = c.world;
   const long long per = (n16 + W - 1) / W;
   const long long b = per * c.rank;
@@ -348,13 +376,7 @@ allgather_kernel(const CommDev c, const PeerPtrs buf, long long n16) {
     for (int r = 0; r < W; ++r)
       if (r != c.rank) reinterpret_cast<uint4*>(buf.p[r])[i] = v;
   }
-  comm_finish(c, e);
-}
-
-__global__ void barrier_kernel(const CommDev c) {
-  const uint32_t e = *c.epoch + 1;
-  comm_start(c, e);
-  comm_finish(c, e);
+  trace_exit(slot);
 }
 
 // Single-rank optimizer step on a flat fp32 arena (W = 1, no flags touched).
@@ -407,12 +429,11 @@ extern "C" int dtdl_comm_create(int rank, int world, void** handle, void** flags
   h->d.world = world;
   DTDL_CHECK_CUDA(cudaGetDevice(&h->device));
   uint32_t* mem = nullptr;
-  // flags + epoch + counter in one allocation: [2*kMaxWorld flags][epoch][counter]
+  // flags + the two epoch words in one allocation: [2*kMaxWorld flags][START epoch][DONE epoch]
   DTDL_CHECK_CUDA(cudaMalloc(&mem, (2 * kMaxWorld + 2) * sizeof(uint32_t)));
   DTDL_CHECK_CUDA(cudaMemset(mem, 0, (2 * kMaxWorld + 2) * sizeof(uint32_t)));
   h->d.flags_local = mem;
-  h->d.epoch = mem + 2 * kMaxWorld;
-  h->d.counter = mem + 2 * kMaxWorld + 1;
+  h->d.epochs = mem + 2 * kMaxWorld;
   h->d.flags_peer[rank] = mem;
   *handle = h;
   *flags_ptr = mem;
@@ -480,6 +501,52 @@ extern "C" int dtdl_enable_peer_access(int dev, int peer) {
   return 0;
 }
 
+static TraceSlot* next_slot(CommHost* h) {
+  if (h->trace == nullptr || h->trace_next >= h->trace_cap) return nullptr;
+  return h->trace + h->trace_next++;
+}
+
+// START exchange in front of a data kernel / DONE exchange behind it (see CommDev).
+static int sync_row(CommHost* h, int row, cudaStream_t stream) {
+  if (h->d.world == 1) return 0;
+  sync_kernel<<<1, 32, 0, stream>>>(h->d, row, next_slot(h));
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+static int sync_before(CommHost* h, cudaStream_t stream) { return sync_row(h, 0, stream); }
+static int sync_after(CommHost* h, cudaStream_t stream) {
+  return h->defer_done ? 0 : sync_row(h, 1, stream);
+}
+
+// defer = 1: the collectives that follow skip their trailing DONE exchange; the caller must issue
+// dtdl_comm_barrier on the same stream before any rank touches the buffers again.  defer = 0 (the
+// default): every collective is self-contained.
+extern "C" int dtdl_comm_defer_done(void* handle, int defer) {
+  reinterpret_cast<CommHost*>(handle)->defer_done = defer ? 1 : 0;
+  return 0;
+}
+
+// Device-side timeline: `base` = device buffer of `capacity` slots of 4 x u64 {t0 ns, t1 ns, kind,
+// bytes} (zero it first); every sync / data kernel launched through this handle from now on records
+// into the next slot.  base = NULL switches tracing off.  Kinds: 1 START wait, 2 DONE wait, 3 reduce,
+// 4 NVLS reduce, 5 broadcast, 6 all-gather, 7 user mark.
+extern "C" int dtdl_comm_trace(void* handle, void* base, int capacity) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  h->trace = reinterpret_cast<TraceSlot*>(base);
+  h->trace_cap = base ? capacity : 0;
+  h->trace_next = 0;
+  return 0;
+}
+extern "C" int dtdl_comm_trace_mark(void* handle, int kind, void* stream) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  TraceSlot* s = next_slot(h);
+  if (s == nullptr) return 0;
+  trace_mark_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(s, kind);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+extern "C" int dtdl_comm_trace_count(void* handle) { return reinterpret_cast<CommHost*>(handle)->trace_next; }
+
 static int fill_peers(PeerPtrs* pp, void* const* ptrs, int world, long long offset_bytes) {
   memset(pp, 0, sizeof(*pp));
   for (int r = 0; r < world; ++r) {
@@ -490,10 +557,8 @@ static int fill_peers(PeerPtrs* pp, void* const* ptrs, int world, long long offs
 }
 
 extern "C" int dtdl_comm_barrier(void* handle, void* stream) {
-  CommHost* h = reinterpret_cast<CommHost*>(handle);
-  barrier_kernel<<<1, 32, 0, STREAM(stream)>>>(h->d);
-  DTDL_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  // one DONE-row exchange: every rank has finished everything it enqueued before this call
+  return sync_row(reinterpret_cast<CommHost*>(handle), 1, STREAM(stream));
 }
 
 // Plain all-reduce (sum * scale) of n fp32 elements at byte offset `offset` of
@@ -517,9 +582,10 @@ extern "C" int dtdl_comm_allreduce(void* handle, void* const* grads, void* const
   a.two_shot = two_shot;
   a.scale = scale;
   const int grid = comm_grid(n / 4, h->d.world, two_shot, max_blocks > 0 ? max_blocks : 64);
-  launch_reduce(h->d, a, grid, STREAM(stream));
+  if (sync_before(h, STREAM(stream))) return 1;
+  launch_reduce(h->d, a, grid, STREAM(stream), next_slot(h));
   DTDL_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return sync_after(h, STREAM(stream));
 }
 
 // Fused gradient all-reduce + 1/W + weight decay + SGD-momentum / Adam update.
@@ -546,9 +612,10 @@ extern "C" int dtdl_comm_reduce_update(void* handle, void* const* grads, void* c
   a.two_shot = two_shot;
   a.scale = 1.f;
   const int grid = comm_grid(n / 4, h->d.world, two_shot, max_blocks > 0 ? max_blocks : 64);
-  launch_reduce(h->d, a, grid, STREAM(stream));
+  if (sync_before(h, STREAM(stream))) return 1;
+  launch_reduce(h->d, a, grid, STREAM(stream), next_slot(h));
   DTDL_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return sync_after(h, STREAM(stream));
 }
 
 extern "C" int dtdl_comm_broadcast(void* handle, void* const* bufs, long long offset_bytes,
@@ -562,9 +629,10 @@ extern "C" int dtdl_comm_broadcast(void* handle, void* const* bufs, long long of
   const int cap = max_blocks > 0 ? max_blocks : 64;
   if (g > cap) g = cap;
   if (g < 1) g = 1;
-  broadcast_kernel<<<(int)g, 512, 0, STREAM(stream)>>>(h->d, pp, n16, root);
+  if (sync_before(h, STREAM(stream))) return 1;
+  broadcast_kernel<<<(int)g, 512, 0, STREAM(stream)>>>(h->d, pp, n16, root, next_slot(h));
   DTDL_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return sync_after(h, STREAM(stream));
 }
 
 extern "C" int dtdl_comm_allgather(void* handle, void* const* bufs, long long offset_bytes,
@@ -578,9 +646,10 @@ extern "C" int dtdl_comm_allgather(void* handle, void* const* bufs, long long of
   const int cap = max_blocks > 0 ? max_blocks : 64;
   if (g > cap) g = cap;
   if (g < 1) g = 1;
-  allgather_kernel<<<(int)g, 512, 0, STREAM(stream)>>>(h->d, pp, n16);
+  if (sync_before(h, STREAM(stream))) return 1;
+  allgather_kernel<<<(int)g, 512, 0, STREAM(stream)>>>(h->d, pp, n16, next_slot(h));
   DTDL_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return sync_after(h, STREAM(stream));
 }
 
 extern "C" int dtdl_local_update(float* param, const float* grad, float* mom, float* var,
@@ -610,9 +679,10 @@ extern "C" int dtdl_comm_nvls_allreduce(void* handle, void* mc_src, void* mc_dst
   a.two_shot = 1;
   a.scale = scale;
   const int grid = comm_grid(n / 4, h->d.world, 1, max_blocks > 0 ? max_blocks : 64);
-  nvls_reduce_kernel<<<grid, 512, 0, STREAM(stream)>>>(h->d, a);
+  if (sync_before(h, STREAM(stream))) return 1;
+  nvls_reduce_kernel<<<grid, 512, 0, STREAM(stream)>>>(h->d, a, next_slot(h));
   DTDL_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return sync_after(h, STREAM(stream));
 }
 
 extern "C" int dtdl_comm_nvls_reduce_update(void* handle, void* mc_grads, void* mc_params, float* param,
@@ -637,9 +707,10 @@ extern "C" int dtdl_comm_nvls_reduce_update(void* handle, void* mc_grads, void* 
   a.two_shot = 1;
   a.scale = 1.f;
   const int grid = comm_grid(n / 4, h->d.world, 1, max_blocks > 0 ? max_blocks : 64);
-  nvls_reduce_kernel<<<grid, 512, 0, STREAM(stream)>>>(h->d, a);
+  if (sync_before(h, STREAM(stream))) return 1;
+  nvls_reduce_kernel<<<grid, 512, 0, STREAM(stream)>>>(h->d, a, next_slot(h));
   DTDL_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return sync_after(h, STREAM(stream));
 }
 
 extern "C" int dtdl_comm_nvls_broadcast(void* handle, void* local, void* mc, long long offset_bytes,
@@ -652,9 +723,10 @@ extern "C" int dtdl_comm_nvls_broadcast(void* handle, void* local, void* mc, lon
   const int cap = max_blocks > 0 ? max_blocks : 64;
   if (g > cap) g = cap;
   if (g < 1) g = 1;
+  if (sync_before(h, STREAM(stream))) return 1;
   nvls_broadcast_kernel<<<(int)g, 512, 0, STREAM(stream)>>>(
       h->d, reinterpret_cast<const float*>(reinterpret_cast<char*>(local) + offset_bytes),
-      reinterpret_cast<float*>(reinterpret_cast<char*>(mc) + offset_bytes), n16, root);
+      reinterpret_cast<float*>(reinterpret_cast<char*>(mc) + offset_bytes), n16, root, next_slot(h));
   DTDL_CHECK_CUDA(cudaGetLastError());
-  return 0;
+  return sync_after(h, STREAM(stream));
 }

@@ -115,6 +115,13 @@ def reset_launch_count():
     _launch_count = 0
 
 
+def add_launches(n):
+    """Kernels launched by a native call beyond its ``_LAUNCHES`` entry (the one-CTA flag-exchange
+    kernels around a collective, which depend on world size and mode)."""
+    global _launch_count
+    _launch_count += n
+
+
 def launch_count():
     """Number of this library's kernels launched since ``reset_launch_count()``."""
     return _launch_count

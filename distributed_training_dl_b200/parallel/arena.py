@@ -34,7 +34,7 @@ def _round_up(n, a):
 
 class ParamArena:
     def __init__(self, params, device, peer=None, bucket_cap_mb=25.0, first_bucket_mb=1.0,
-                 local_peers=None, rank=0):
+                 local_peers=None, rank=0, last_bucket_mb=4.0):
         """``peer``: PeerComm (multi-process) or None; ``local_peers``: list of PeerComm for the
         single-process multi-GPU engine together with ``rank`` selecting this replica."""
         self.device = torch.device(device)
@@ -55,6 +55,23 @@ class ParamArena:
                 cap = int(bucket_cap_mb * (1 << 20)) // 4
         if cur:
             self.buckets.append(Bucket(len(self.buckets), cur_start, off - cur_start, cur))
+        # The last bucket becomes ready only when backward ends, so its collective (and the update and
+        # re-pack behind it) has nothing to hide under: keep it small.  Its parameters are the first
+        # layers of the model, which are the ones that finish last.
+        tail_cap = int(last_bucket_mb * (1 << 20)) // 4
+        if self.buckets and last_bucket_mb > 0 and self.buckets[-1].numel > tail_cap and len(self.buckets[-1].params) > 1:
+            last = self.buckets.pop()
+            tail, tail_n = [], 0
+            for p in reversed(last.params):
+                n = _round_up(p.numel(), ALIGN)
+                if tail and tail_n + n > tail_cap:
+                    break
+                tail.insert(0, p)
+                tail_n += n
+            head = last.params[: len(last.params) - len(tail)]
+            if head:
+                self.buckets.append(Bucket(len(self.buckets), last.offset, last.numel - tail_n, head))
+            self.buckets.append(Bucket(len(self.buckets), last.offset + last.numel - tail_n, tail_n, tail))
         self.numel = max(off, ALIGN)
         self.bucket_of = {id(p): b.index for b in self.buckets for p in b.params}
         self.param_buf = self.grad_buf = None

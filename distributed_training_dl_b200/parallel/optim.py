@@ -198,6 +198,8 @@ class _FusedBase(torch.optim.Optimizer):
         if r is not None and hasattr(r, "repack_all"):
             r.repack_all(self._pack_caches)
             return
+        if r is not None and getattr(r, "packs_current", False):
+            return    # every bucket re-packed its own layers on the communication stream
         mods = r.packed_modules if r is not None else self._own_packed
         if mods:
             pack_weights(mods, self._pack_caches[0])

@@ -161,6 +161,8 @@ class PeerComm:
         self.use_nvls = False
         self.nvls_min_bytes = int(os.environ.get("DTDL_NVLS_MIN_BYTES", "0"))
         self._fdchan = None
+        self._deferred = False
+        self._trace = None
 
     # ------------------------------------------------------------------ construction
     @classmethod
@@ -412,6 +414,53 @@ class PeerComm:
 
     def barrier(self, stream=None):
         nv.call("comm_barrier", self.handle, self._stream(stream))
+        if self.world == 1:
+            nv.add_launches(-1)
+
+    def _count_sync(self):
+        # flag-exchange kernels around the data kernel just launched: START always, DONE unless deferred
+        if self.world > 1:
+            nv.add_launches(1 if self._deferred else 2)
+
+    def defer_done(self, on: bool):
+        """``True``: the collectives that follow skip their trailing cross-GPU "done" exchange; close
+        the sequence with ONE ``barrier()`` on the same stream before any rank touches the buffers
+        again (what the gradient reducer does per training step).  ``False``: every collective is
+        self-contained again."""
+        self._deferred = bool(on)
+        nv.lib().dtdl_comm_defer_done(self.handle, 1 if on else 0)
+
+    # ------------------------------------------------------------------ device-side timeline
+    TRACE_KINDS = {1: "wait(start)", 2: "wait(done)", 3: "reduce", 4: "nvls_reduce", 5: "broadcast",
+                   6: "allgather", 7: "mark"}
+
+    def trace_begin(self, capacity: int = 256):
+        """Every sync / data kernel launched through this communicator from now on stamps its first
+        block's start and last block's end (``%globaltimer``) into a device buffer -- also when the
+        launches are replayed from a CUDA graph.  Call before the step is captured / run."""
+        with torch.cuda.device(self.device):
+            self._trace = torch.zeros((capacity, 4), dtype=torch.int64, device=self.device)
+        nv.lib().dtdl_comm_trace(self.handle, ctypes.c_void_p(self._trace.data_ptr()), capacity)
+
+    def trace_mark(self, stream=None):
+        """A time stamp on ``stream`` (e.g. right after the last backward kernel)."""
+        nv.call("comm_trace_mark", self.handle, 7, self._stream(stream))
+
+    def trace_end(self):
+        nv.lib().dtdl_comm_trace(self.handle, None, 0)
+
+    def trace_rows(self):
+        """[(kind, t0_us, t1_us, bytes)] of the last execution of the traced launches, times relative
+        to the earliest start."""
+        if getattr(self, "_trace", None) is None:
+            return []
+        torch.cuda.synchronize(self.device)
+        t = self._trace.cpu()
+        rows = [(int(k), int(a), int(b), int(n)) for a, b, k, n in t.tolist() if k]
+        if not rows:
+            return []
+        t_min = min(a for _, a, _, _ in rows)
+        return [(self.TRACE_KINDS.get(k, str(k)), (a - t_min) / 1e3, (b - t_min) / 1e3, n) for k, a, b, n in rows]
 
     def allreduce(self, buf: SymmBuffer, offset_bytes: int, numel: int, scale: float = 1.0,
                   two_shot=None, dst: SymmBuffer = None, stream=None, max_blocks=None):
@@ -428,9 +477,11 @@ class PeerComm:
         if ts == 2:
             nv.call("comm_nvls_allreduce", self.handle, ctypes.c_void_p(buf.mc_ptr), ctypes.c_void_p(dst.mc_ptr),
                     offset_bytes, numel, scale, max_blocks or self.max_blocks, self._stream(stream))
+            self._count_sync()
             return
         nv.call("comm_allreduce", self.handle, buf.ptr_array, dst.ptr_array, offset_bytes, numel, scale, ts,
                 max_blocks or self.max_blocks, self._stream(stream))
+        self._count_sync()
 
     def reduce_update(self, grads: SymmBuffer, params: SymmBuffer, mom, var, hyper, offset_bytes: int,
                       numel: int, opt: int, two_shot=None, stream=None, max_blocks=None):
@@ -442,23 +493,28 @@ class PeerComm:
             nv.call("comm_nvls_reduce_update", self.handle, ctypes.c_void_p(grads.mc_ptr),
                     ctypes.c_void_p(params.mc_ptr), ctypes.c_void_p(params.local_ptr), nv.ptr(mom), nv.ptr(var),
                     nv.ptr(hyper), offset_bytes, numel, opt, max_blocks or self.max_blocks, self._stream(stream))
+            self._count_sync()
             return
         nv.call("comm_reduce_update", self.handle, grads.ptr_array, params.ptr_array, nv.ptr(mom),
                 nv.ptr(var), nv.ptr(hyper), offset_bytes, numel, opt, ts, max_blocks or self.max_blocks,
                 self._stream(stream))
+        self._count_sync()
 
     def broadcast(self, buf: SymmBuffer, offset_bytes: int, nbytes: int, root: int = 0, stream=None,
                   max_blocks=None):
         if self._nvls_ok(buf, buf, nbytes):
             nv.call("comm_nvls_broadcast", self.handle, ctypes.c_void_p(buf.local_ptr), ctypes.c_void_p(buf.mc_ptr),
                     offset_bytes, nbytes, root, max_blocks or self.max_blocks, self._stream(stream))
+            self._count_sync()
             return
         nv.call("comm_broadcast", self.handle, buf.ptr_array, offset_bytes, nbytes, root,
                 max_blocks or self.max_blocks, self._stream(stream))
+        self._count_sync()
 
     def allgather(self, buf: SymmBuffer, offset_bytes: int, nbytes: int, stream=None, max_blocks=None):
         nv.call("comm_allgather", self.handle, buf.ptr_array, offset_bytes, nbytes,
                 max_blocks or self.max_blocks, self._stream(stream))
+        self._count_sync()
 
     def close(self):
         torch.cuda.synchronize(self.device)

@@ -53,6 +53,19 @@ class Reducer:
         self.buffers = BufferArena(list(module.buffers()), self.device, peer=self.peer)
         self.broadcast_buffers = broadcast_buffers
         self.packed_modules = packed_layers(module) if self.device.type == "cuda" else []
+        # conv / linear layers whose weight lives in bucket b: their operand packs are rebuilt on the
+        # communication stream right behind b's update, under the rest of backward (packs_in_buckets
+        # tells the optimizer that step() has nothing left to re-pack)
+        self.packs_in_buckets = self.device.type == "cuda"
+        self._bucket_packed = {b.index: [] for b in self.arena.buckets}
+        for m in self.packed_modules:
+            b = self.arena.bucket_of.get(id(m.weight))
+            if b is not None and getattr(m, "pack_src", None) is None:
+                self._bucket_packed[b].append(m)
+        self._bucket_pack_cache = {b.index: {} for b in self.arena.buckets}
+        self._deferred = False
+        self._updated_buckets = 0
+        self.packs_current = False     # True after a step whose buckets all re-packed their layers
         self.optimizer = None
         self.state_sharded = False
         self.require_sync = True
@@ -88,13 +101,24 @@ class Reducer:
             m._packed_version = None
 
     def sync_buffers(self):
-        """Per-forward BatchNorm running-stat sync from rank 0 (K-C2)."""
+        """Per-step BatchNorm running-stat sync from rank 0 (K-C2).
+
+        torch.distributed back ends: at the start of every forward, as DDP does.  Peer back end: the
+        broadcast rides on the communication stream in front of the step's first bucket (see
+        ``_launch_impl``), i.e. it happens once this step's forward has updated rank 0's statistics
+        and is overlapped with backward; every rank therefore starts the next forward from rank 0's
+        values -- the state DDP's broadcast-before-forward produces -- without a cross-GPU wait on the
+        critical path of the forward pass."""
         if self.world == 1 or not self.broadcast_buffers or self.buffers.nbytes <= 16:
             return
-        if self.peer is not None:
-            self.peer.broadcast(self.buffers.buf, 0, self.buffers.nbytes, root=0, max_blocks=4)
-        else:
+        if self.peer is None:
             dist.broadcast(self.buffers.bytes, src=0, group=self.comm.group)
+
+    def _sync_buffers_on_comm_stream(self):
+        if self.world == 1 or not self.broadcast_buffers or self.buffers.nbytes <= 16:
+            return
+        self.peer.broadcast(self.buffers.buf, 0, self.buffers.nbytes, root=0, max_blocks=4,
+                            stream=self.comm_stream)
 
     # ------------------------------------------------------------------ backward-time reduction
     def prepare(self):
@@ -108,6 +132,8 @@ class Reducer:
         self._user_stream = torch.cuda.current_stream(self.device) if self.device.type == "cuda" else None
         self._next = 0
         self._launched_any = False
+        self._updated_buckets = 0
+        self.packs_current = False
         if self.optimizer is not None:
             self.optimizer.refresh_hyper()
 
@@ -143,6 +169,9 @@ class Reducer:
 
     def _backward_done(self):
         self._callback_queued = False
+        fn.join_side_streams()   # idempotent: the weight-gradient branch joins the main chain first
+        if self.peer is not None and self.peer._trace is not None:
+            self.peer.trace_mark(stream=getattr(self, "_user_stream", None))   # "backward has ended"
         if not self.require_sync:
             return
         if self.optimizer is None:
@@ -164,20 +193,37 @@ class Reducer:
             if _NVTX:
                 torch.cuda.nvtx.range_pop()
 
+    def _join_producers(self):
+        """The communication stream waits for everything that may have produced this bucket's
+        gradients: the stream this hook runs on, the user's stream, and the side stream that carries
+        weight gradients during graph capture."""
+        streams = [torch.cuda.current_stream(self.device)]
+        for extra in (getattr(self, "_user_stream", None), fn.forked_side_stream(self.device)):
+            if extra is not None and all(extra != s for s in streams):
+                streams.append(extra)
+        for s in streams:
+            ev = torch.cuda.Event()
+            ev.record(s)
+            self.comm_stream.wait_event(ev)
+
+    def _repack_bucket(self, bucket):
+        mods = self._bucket_packed.get(bucket.index)
+        if mods:
+            from ..ops.modules import pack_weights
+            with torch.cuda.stream(self.comm_stream):
+                pack_weights(mods, self._bucket_pack_cache[bucket.index])
+
     def _launch_impl(self, bucket):
         off_b, n = bucket.offset * 4, bucket.numel
         a = self.arena
         if self.peer is not None and self.world > 1:
-            # the bucket's gradients may come from three places: the stream this hook runs on, the
-            # user's stream, and the side stream that carries weight gradients during graph capture
-            streams = [torch.cuda.current_stream(self.device)]
-            for extra in (getattr(self, "_user_stream", None), fn.forked_side_stream(self.device)):
-                if extra is not None and all(extra != s for s in streams):
-                    streams.append(extra)
-            for s in streams:
-                ev = torch.cuda.Event()
-                ev.record(s)
-                self.comm_stream.wait_event(ev)
+            self._join_producers()
+            if not self._launched_any:
+                # first bucket of the step: from here to finish_step the collectives run back to back
+                # on the communication stream and share ONE closing "done" exchange
+                self.peer.defer_done(True)
+                self._deferred = True
+                self._sync_buffers_on_comm_stream()
             timed = self.bucket_timing and not torch.cuda.is_current_stream_capturing()
             if timed:
                 e0 = torch.cuda.Event(enable_timing=True)
@@ -190,6 +236,7 @@ class Reducer:
                 self.state_sharded = self.state_sharded or bool(two)
                 self.peer.reduce_update(a.grad_buf, a.param_buf, m, v, opt._hyper_dev, off_b, n,
                                         opt.opt_code, two_shot=two, stream=self.comm_stream)
+                self._repack_bucket(bucket)
             else:
                 self.peer.allreduce(a.grad_buf, off_b, n, scale=1.0 / self.world, stream=self.comm_stream)
             if timed:
@@ -204,6 +251,20 @@ class Reducer:
             t0 = time.perf_counter() if self.bucket_timing else None
             work = dist.all_reduce(g, group=self.comm.group, async_op=True)
             self._works.append((work, bucket, t0))
+        elif self._fused() and self.device.type == "cuda":
+            # one GPU: the bucket's optimizer update and re-pack run on the side stream as soon as
+            # its gradients are complete, under the rest of backward, instead of after it
+            self._join_producers()
+            opt = self.optimizer
+            m = opt._state_flat[opt.state_names[0]]
+            v = opt._state_flat[opt.state_names[1]] if len(opt.state_names) > 1 else None
+            sl = slice(bucket.offset, bucket.offset + n)
+            from .. import _native as nv
+            nv.call("local_update", nv.ptr(a.param_flat[sl]), nv.ptr(a.grad_flat[sl]), nv.ptr(m[sl]),
+                    nv.ptr(v[sl]) if v is not None else 0, nv.ptr(opt._hyper_dev), n, opt.opt_code,
+                    self.comm_stream.cuda_stream)
+            self._repack_bucket(bucket)
+            self._updated_buckets += 1
         self._launched_any = True
 
     def flush(self):
@@ -219,9 +280,15 @@ class Reducer:
         self.flush()
         a = self.arena
         if self.peer is not None and self.world > 1:
+            if self._deferred:
+                # the step's single "done" exchange: no rank reads or writes our arenas after this
+                self.peer.barrier(stream=self.comm_stream)
+                self.peer.defer_done(False)
+                self._deferred = False
             torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
             if getattr(self, "_user_stream", None) is not None:
                 self._user_stream.wait_stream(self.comm_stream)
+            self.packs_current = bool(fused and self.require_sync and self.packs_in_buckets)
         elif self.world > 1:
             for work, bucket, t0 in self._works:
                 work.wait()
@@ -233,7 +300,15 @@ class Reducer:
                     self.optimizer._update_torch(a.grad_flat, bucket.offset, bucket.numel)
             self._works = []
         if fused and self.world == 1:
-            self.optimizer._local_update()
+            if self._updated_buckets == len(a.buckets) and self.comm_stream is not None:
+                torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+                if getattr(self, "_user_stream", None) is not None:
+                    self._user_stream.wait_stream(self.comm_stream)
+                self.packs_current = True
+            else:
+                assert self._updated_buckets == 0, "a step updated only some of its buckets"
+                self.optimizer._local_update()
+                self.packs_current = False
         self._pending = None
 
     def wait(self):

@@ -171,6 +171,18 @@ int dtdl_enable_peer_access(int dev, int peer);
  * -1: query failed.  The shipped collectives are the P2P variants; multicast ones are gated on this. */
 int dtdl_multicast_supported(int device);
 int dtdl_comm_barrier(void* handle, void* stream);
+/* Each collective = START exchange (one-CTA kernel) + data kernel + DONE exchange (one-CTA kernel).
+ * defer = 1 drops the DONE exchange of the collectives that follow: a training step then closes all
+ * its buckets with ONE dtdl_comm_barrier on the same stream (buckets touch disjoint memory).  The
+ * reference's DDP overlaps all but the last bucket the same way
+ * (pytorch/distributed_data_parallel.py:128-133). */
+int dtdl_comm_defer_done(void* handle, int defer);
+/* Device-side timeline of the collectives (works inside a replayed CUDA graph): `base` = zeroed device
+ * buffer of `capacity` slots of 4 x u64 {start ns, end ns, kind, bytes}; NULL = off.  Kinds: 1 START
+ * wait, 2 DONE wait, 3 reduce, 4 NVLS reduce, 5 broadcast, 6 all-gather, 7 mark. */
+int dtdl_comm_trace(void* handle, void* base, int capacity);
+int dtdl_comm_trace_mark(void* handle, int kind, void* stream);
+int dtdl_comm_trace_count(void* handle);
 /* dst[r] = scale * sum over ranks of grads[r].  two_shot 0 = one-shot (every rank reads all peers;
  * needs dst != grads), 1 = two-shot; an in-place call (dst == grads) always runs two-shot. */
 int dtdl_comm_allreduce(void* handle, void* const* grads, void* const* dst, long long offset_bytes,
