@@ -129,6 +129,63 @@ class PrintLR(Callback):
             print(f"\nLearning rate for epoch {epoch + 1} is {self.model.optimizer.param_groups[0]['lr']}")
 
 
+class TensorBoard(Callback):
+    """``tf.keras.callbacks.TensorBoard(log_dir, histogram_freq=1)`` as all three TF2 scripts register
+    it (tensorflow2/mnist_single.py:72-76, mnist_multi_worker_strategy.py:79-83): per-epoch scalars
+    (loss / accuracy / val_*) and, every ``histogram_freq`` epochs, a histogram of every weight
+    tensor.  Event files come from ``torch.utils.tensorboard`` when the ``tensorboard`` package is
+    importable; otherwise the same records go to ``<log_dir>/events.jsonl`` (one JSON object per line,
+    histograms as 30-bin counts).  Only rank 0 writes (the reference lets every worker write into the
+    same directory: SURVEY.md Q14)."""
+
+    def __init__(self, log_dir="./logs", histogram_freq=0, bins=30):
+        self.log_dir, self.histogram_freq, self.bins = log_dir, int(histogram_freq), bins
+        self._writer = self._jsonl = None
+
+    def _open(self):
+        if self._writer is not None or self._jsonl is not None:
+            return
+        os.makedirs(self.log_dir, exist_ok=True)
+        try:
+            from torch.utils.tensorboard import SummaryWriter
+            self._writer = SummaryWriter(log_dir=self.log_dir)
+        except Exception:  # noqa: BLE001 - tensorboard not installed: plain JSON lines instead
+            self._jsonl = open(os.path.join(self.log_dir, "events.jsonl"), "a")
+
+    def on_epoch_end(self, epoch, logs=None):
+        if get_rank() != 0:
+            return
+        self._open()
+        step = epoch + 1
+        scalars = {k: float(v) for k, v in (logs or {}).items() if k != "time"}
+        hist = {}
+        if self.histogram_freq and step % self.histogram_freq == 0:
+            for name, p in self.model._bare().named_parameters():
+                hist[name] = p.detach().float().cpu()
+        if self._writer is not None:
+            for k, v in scalars.items():
+                self._writer.add_scalar("epoch_" + k, v, step)
+            for name, t in hist.items():
+                self._writer.add_histogram(name, t, step)
+            self._writer.flush()
+        else:
+            import json
+            rec = {"epoch": step, "scalars": scalars, "histograms": {}}
+            for name, t in hist.items():
+                lo, hi = float(t.min()), float(t.max())
+                rec["histograms"][name] = {"min": lo, "max": hi,
+                                           "counts": torch.histc(t, bins=self.bins, min=lo, max=hi).int().tolist()}
+            self._jsonl.write(json.dumps(rec) + "\n")
+            self._jsonl.flush()
+
+    def close(self):
+        if self._writer is not None:
+            self._writer.close()
+        if self._jsonl is not None:
+            self._jsonl.close()
+        self._writer = self._jsonl = None
+
+
 class History(Callback):
     def __init__(self):
         self.history = {}

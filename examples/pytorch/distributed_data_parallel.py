@@ -6,6 +6,18 @@ Launch any of these ways:
   srun -n 16 python distributed_data_parallel.py                            (SLURM)
   python distributed_data_parallel.py --init-method tcp://c1:20201 --rank r --world-size W
   python distributed_data_parallel.py --spawn 8                             (mp.spawn, one node)
+
+Batch size.  ``--batch-size`` is the batch of ONE process, i.e. of one GPU: the global
+batch is ``batch_size x world_size`` and every epoch has ``len(dataset) / (batch_size x world_size)``
+steps.  The reference divides the flag by the GPUs visible to the process instead
+(pytorch/distributed_data_parallel.py:71, ``args.batch_size = int(args.batch_size / ngpus_per_node)``);
+its README launches one process per shell with a single visible GPU, where that division is by one,
+so the effective rule is the same: 64 per process, 64 x W globally.  Launchers that make all GPUs
+visible to every process (torchrun, ``--spawn``) therefore do NOT shrink the per-process batch here --
+pass ``--batch-size 8`` yourself if you want a global batch of 64 on 8 GPUs.
+
+``--precision tf32`` trains at the reference's own precision (fp32 tensors, TF32 convolutions),
+``bf16`` (default) is the fast mode.
 """
 import os
 import sys
@@ -22,7 +34,9 @@ def main_worker(local_rank, args):
     logger = dtdl.utils.RankLogger()
     logger.info(f"Use device {comm.device} for training")
     torch.manual_seed(args.seed)
-    net = dtdl.wrap(dtdl.models.pyramidnet().to(comm.device), comm=comm)
+    net = dtdl.wrap(dtdl.models.pyramidnet().to(comm.device), comm=comm, dtype=args.precision)
+    logger.info(f"per-process batch {args.batch_size}, global batch {args.batch_size * comm.size} "
+                f"({comm.size} process(es)); precision {args.precision}")
     logger.info(f"The number of parameters of model is {sum(p.numel() for p in net.parameters())}")
     dataset = cifar_dataset(args)
     sampler = dtdl.DistributedSampler(dataset)
@@ -53,6 +67,8 @@ def main_worker(local_rank, args):
 def main():
     parser = pytorch_flags("B200-native CIFAR-10 training, one process per GPU", distributed=True)
     parser.add_argument("--spawn", type=int, default=0, help="start N local worker processes")
+    parser.add_argument("--precision", default="bf16", choices=["bf16", "tf32"],
+                        help="bf16 (fast) or tf32 = fp32 tensors with TF32 convolutions, the reference's precision")
     parser.add_argument("--bucket-timing", action="store_true",
                         help="report per-bucket all-reduce time and bus bandwidth after each epoch")
     args = parser.parse_args()

@@ -45,7 +45,8 @@ def train_and_eval(args, strategy):
                       learning_rate=args.learning_rate)
     model.summary()
     model.fit(xt, yt, batch_size=args.batch_size, epochs=args.epochs,
-              callbacks=[ks.ModelCheckpoint(filepath=ckpt, save_weights_only=True), ks.PrintLR()],
+              callbacks=[ks.TensorBoard(log_dir=args.train_dir, histogram_freq=1),
+                         ks.ModelCheckpoint(filepath=ckpt, save_weights_only=True), ks.PrintLR()],
               validation_data=(xv, yv))
     latest = ks.latest_checkpoint(args.train_dir)
     if latest:

@@ -211,6 +211,9 @@ def ddp_training(i, world, outdir, use_graph, nvls=False):
     chk = torch.cat([p.detach().flatten()[:64] for p in net.parameters()]).cpu()
     alls = comm.allgather_object(chk)
     assert all(torch.equal(alls[0], a) for a in alls), "replicas diverged"
+    # K-C2 on the peer path: after a step every rank holds rank 0's BatchNorm running statistics
+    rs = comm.allgather_object(torch.cat([b.detach().float().flatten() for b in net.module.buffers()]).cpu())
+    assert all(torch.equal(rs[0], r) for r in rs), "BatchNorm running statistics differ between ranks"
     # optimizer state in torch format after a sharded (two-shot) update
     sd = opt.state_dict()
     mb = comm.allgather_object(sd["state"][0]["momentum_buffer"].flatten()[:16].cpu())
@@ -393,3 +396,66 @@ def ddp_variants(i, world, outdir, backend):
         assert all(torch.equal(alls[0], a) for a in alls), (backend, opt_kind, max((alls[0] - a).abs().max().item() for a in alls))
     _ok(outdir, i)
     dtdl.shutdown()
+
+
+def frontends_multi_gpu(outdir):
+    """Single process, all visible GPUs, through the Keras- and Chainer-shaped front ends:
+    MirroredStrategy (Keras-Adam fused into DataParallelStep), load_weights re-syncing every replica,
+    and ParallelUpdater inside a Trainer (SURVEY.md DP-c, DP-e)."""
+    from distributed_training_dl_b200 import strategy as ks
+    from distributed_training_dl_b200 import trainer as ch
+    from distributed_training_dl_b200.models import MLP, MnistCNN
+    ndev = torch.cuda.device_count()
+    g = torch.Generator().manual_seed(0)
+    y = torch.randint(0, 10, (512,), generator=g)
+    x = torch.randn((512, 1, 28, 28), generator=g) * 0.1 + (y.float().view(-1, 1, 1, 1) - 4.5) / 3
+    # --- MirroredStrategy.fit on all GPUs: global batch split over replicas, Adam (Keras epsilon) fused
+    strategy = ks.MirroredStrategy()
+    assert strategy.num_replicas_in_sync == ndev
+    torch.manual_seed(1)
+    with strategy.scope():
+        model = ks.Model(MnistCNN())
+        model.compile(optimizer="adam", loss="sparse_categorical_crossentropy", metrics=["accuracy"])
+    ckpt = os.path.join(outdir, "ckpt_{epoch}")
+    hist = model.fit(x, y, batch_size=64, epochs=3, verbose=0, validation_data=(x[:128], y[:128]),
+                     callbacks=[ks.ModelCheckpoint(ckpt)])
+    assert hist.history["loss"][-1] < 0.7 * hist.history["loss"][0], hist.history["loss"]
+    dp = model.module
+    assert len(dp.arenas) == ndev
+    ref = dp.arenas[0].param_flat.cpu()
+    assert all(torch.equal(ref, a.param_flat.cpu()) for a in dp.arenas[1:]), "replicas diverged under fit()"
+    # the fused Adam matches torch.optim.Adam(eps=1e-7 inside the sqrt's sum, Keras placement) closely enough
+    # that a 3-epoch run reaches a low loss; exact arithmetic is covered by the collectives test
+    before = model.evaluate(x, y)
+    # --- load_weights into the live model: every replica (and its operand packs) must follow
+    with strategy.scope():
+        fresh = ks.Model(MnistCNN()).compile()
+    fresh.fit(x[:64], y[:64], batch_size=64, epochs=1, verbose=0)      # graph captured, packs exist
+    fresh.load_weights(ks.latest_checkpoint(outdir))
+    dpf = fresh.module
+    ref = dpf.arenas[0].param_flat.cpu()
+    assert all(torch.equal(ref, a.param_flat.cpu()) for a in dpf.arenas[1:]), "load_weights left replicas behind"
+    after = fresh.evaluate(x, y)
+    assert abs(before[0] - after[0]) < 2e-2 * max(1.0, before[0]) and abs(before[1] - after[1]) < 0.02, (before, after)
+    # one more training step from the loaded weights must start from the loaded loss, not the old packs
+    h2 = fresh.fit(x, y, batch_size=128, epochs=1, verbose=0, shuffle=False)
+    assert h2.history["loss"][0] < 2.0 * max(before[0], 0.05) + 0.2, (h2.history["loss"], before)
+    # --- Chainer-shaped ParallelUpdater (train_mnist_gpu.py:52-62,87-93)
+    xs = x.reshape(512, 784)
+    data = list(zip(xs, y))
+    torch.manual_seed(2)
+    clf = ch.Classifier(MLP(64, 10))
+    opt = ch.Adam().setup(clf)
+    devices = {"main": 0, "second": 1} if ndev >= 2 else {"main": 0}
+    updater = ch.ParallelUpdater(ch.SerialIterator(data, 64), opt, devices=devices)
+    tr = ch.Trainer(updater, (2, "epoch"), out=os.path.join(outdir, "chainer"))
+    tr.extend(ch.LogReport())
+    tr.run()
+    assert updater.iteration == 16
+    assert tr.observation["main/loss"] == tr.observation["main/loss"]
+    wrapped = updater.wrapped
+    ref = wrapped.arenas[0].param_flat.cpu()
+    assert all(torch.equal(ref, a.param_flat.cpu()) for a in wrapped.arenas[1:]), "ParallelUpdater replicas diverged"
+    log = tr.observation
+    assert log["main/accuracy"] > 0.5, log
+    open(os.path.join(outdir, "ok_fe"), "w").write("ok")

@@ -115,9 +115,51 @@ def ddp_pyramidnet(i, world, port, outdir):
     chk = torch.cat([p.detach().flatten()[:64] for p in net.parameters()])
     allc = comm.allgather_object(chk)
     assert all(torch.equal(allc[0], c) for c in allc)
-    net(torch.randn(2, 3, 32, 32))
-    rm = comm.allgather_object(net.module.bn1.running_mean.clone())
+    # K-C2: whatever a rank's running statistics hold, the per-forward sync makes them rank 0's
+    with torch.no_grad():
+        net.module.bn1.running_mean.fill_(float(i + 1))
+        net.module.bn1.running_var.fill_(float(10 * (i + 1)))
+    net.reducer.sync_buffers()
+    rm = comm.allgather_object((net.module.bn1.running_mean.clone(), net.module.bn1.running_var.clone()))
+    for mean, var in rm:
+        assert torch.equal(mean, torch.full_like(mean, 1.0)) and torch.equal(var, torch.full_like(var, 10.0))
     open(os.path.join(outdir, f"ok_{i}"), "w").write("ok")
+    dtdl.shutdown()
+
+
+def multi_worker_fit(i, world, port, outdir):
+    """MultiWorkerMirroredStrategy.fit on 2 workers (tensorflow2/mnist_multi_worker_strategy.py:14-29,
+    85-96): host-list rendezvous, every worker trains on its strided shard with the global batch split
+    over the workers, replicas stay identical, the loss falls, rank 0 alone writes checkpoints and
+    TensorBoard records."""
+    from distributed_training_dl_b200 import strategy as ks
+    from distributed_training_dl_b200.models import MnistCNN
+    torch.set_num_threads(2)
+    for k in ("RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "LOCAL_RANK"):
+        os.environ.pop(k, None)
+    hosts = ",".join(f"127.0.0.1:{port + r}" for r in range(world))
+    strategy = ks.MultiWorkerMirroredStrategy(worker_hosts=hosts, task_index=i, backend="gloo")
+    assert strategy.num_replicas_in_sync == world
+    g = torch.Generator().manual_seed(0)
+    y = torch.randint(0, 10, (256,), generator=g)
+    x = torch.randn((256, 1, 28, 28), generator=g) * 0.1 + (y.float().view(-1, 1, 1, 1) - 4.5) / 3
+    torch.manual_seed(100 + i)      # different initial weights per worker: wrap() must broadcast rank 0's
+    with strategy.scope():
+        model = ks.Model(MnistCNN())
+        model.compile(optimizer="adam", loss="sparse_categorical_crossentropy", metrics=["accuracy"])
+    logdir = os.path.join(outdir, "tb")
+    hist = model.fit(x, y, batch_size=64, epochs=3, verbose=0, validation_data=(x[:64], y[:64]),
+                     callbacks=[ks.TensorBoard(log_dir=logdir, histogram_freq=1),
+                                ks.ModelCheckpoint(os.path.join(outdir, "ckpt_{epoch}"))])
+    assert hist.history["loss"][-1] < hist.history["loss"][0], hist.history["loss"]
+    comm = strategy.comm
+    chk = torch.cat([p.detach().flatten()[:64] for p in model.module.parameters()])
+    allc = comm.allgather_object(chk)
+    assert all(torch.equal(allc[0], c) for c in allc), "workers diverged"
+    comm.barrier()
+    assert os.path.exists(os.path.join(outdir, "ckpt_3")) and os.listdir(logdir)
+    open(os.path.join(outdir, f"ok_{i}"), "w").write("ok")
+    import distributed_training_dl_b200 as dtdl
     dtdl.shutdown()
 
 

@@ -83,3 +83,16 @@ def test_ddp_backends_optimizers_no_sync(tmp_path, backend):
     world = _world()
     dtdl.spawn(ddp_variants, nprocs=world, args=(world, str(tmp_path), backend))
     assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
+
+
+def test_frontends_on_all_gpus(tmp_path):
+    """MirroredStrategy.fit, load_weights replica re-sync and ParallelUpdater on >= 2 GPUs."""
+    _world()
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    code = f"import sys; sys.path.insert(0, {here!r}); import _gpu_workers as w; w.frontends_multi_gpu({str(tmp_path)!r})"
+    env = dict(os.environ)
+    env["CUDA_VISIBLE_DEVICES"] = ",".join(str(i) for i in range(min(torch.cuda.device_count(), 2)))
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=900, env=env)
+    assert res.returncode == 0 and os.path.exists(tmp_path / "ok_fe"), res.stdout[-2000:] + res.stderr[-4000:]

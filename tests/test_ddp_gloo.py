@@ -6,7 +6,7 @@ import pytest
 import distributed_training_dl_b200 as dtdl
 from distributed_training_dl_b200.utils import free_port
 
-from _workers import ddp_equivalence, ddp_pyramidnet, fd_channel, slurm_and_hosts_init
+from _workers import ddp_equivalence, ddp_pyramidnet, fd_channel, multi_worker_fit, slurm_and_hosts_init
 
 
 @pytest.mark.parametrize("init_kind", ["tcp", "env"])
@@ -34,4 +34,11 @@ def test_fd_channel(tmp_path, world):
 def test_init_from_slurm_env_and_host_list(tmp_path, kind):
     world = 2
     dtdl.spawn(slurm_and_hosts_init, nprocs=world, args=(world, free_port(), str(tmp_path), kind), set_env=False)
+    assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
+
+
+def test_multi_worker_mirrored_strategy_fit(tmp_path):
+    """DP-d: Model.fit under MultiWorkerMirroredStrategy with two workers."""
+    world = 2
+    dtdl.spawn(multi_worker_fit, nprocs=world, args=(world, free_port(), str(tmp_path)), set_env=False)
     assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))

@@ -25,8 +25,11 @@ def test_keras_style_fit_checkpoint_evaluate(tmp_path):
         model = ks.Model(MnistCNN())
         model.compile(optimizer="adam", loss="sparse_categorical_crossentropy", metrics=["accuracy"])
     ckpt = os.path.join(tmp_path, "ckpt_{epoch}")
-    hist = model.fit(x, y, batch_size=64, epochs=3, callbacks=[ks.ModelCheckpoint(ckpt), ks.PrintLR()],
+    tb = ks.TensorBoard(log_dir=os.path.join(tmp_path, "tb"), histogram_freq=1)
+    hist = model.fit(x, y, batch_size=64, epochs=3, callbacks=[tb, ks.ModelCheckpoint(ckpt), ks.PrintLR()],
                      validation_data=(x[:64], y[:64]), verbose=0)
+    tb.close()
+    assert os.listdir(os.path.join(tmp_path, "tb")), "the TensorBoard callback wrote nothing"
     assert hist.history["loss"][-1] < hist.history["loss"][0]
     assert "val_accuracy" in hist.history
     latest = ks.latest_checkpoint(str(tmp_path))

@@ -223,7 +223,8 @@ def test_models_match_cpu_oracle():
     shallow = lambda: PyramidNet(num_layers=3, alpha=45.0)  # noqa: E731
     # (model, input shape, loss tolerance, minimum gradient cosine).  bf16 activation storage
     # noise accumulates with depth (measured: 0.995 -> 0.985 over 6 blocks, 0.976 -> 0.885 over
-    # 51 blocks, norm ratio 1.00 throughout: tools/debug_depth.py), hence the per-model floor.
+    # 51 blocks, norm ratio 1.00 throughout), hence the per-model floor.  The fp32-activation mode has no such
+    # noise: tests/test_tf32_gpu.py checks every gradient of the full net, BatchNorm included, at 0.95.
     # The 6-block net's smallest per-channel BN gradients land between 0.963 and 0.975 from run to
     # run (batch 8; the float atomics of the statistics reorder, a pre-activation rounds across
     # zero differently), so its floor is 0.95.
@@ -310,7 +311,7 @@ def test_resnet50_whole_model():
     """Whole ResNet-50: loss agrees with the CPU fp32 model and the head gradients match.
     Deeper gradients of a RANDOM-INIT ResNet-50 are chaotic under bf16 rounding -- stock
     torchvision + bf16 autocast gives cosine 0.12 (conv1) .. 0.39 (layer4) against its own fp32
-    run (tools/debug_resnet3.py) -- so they are checked block by block above instead."""
+    run (measured in round 1) -- so they are checked block by block above instead."""
     import copy
     from distributed_training_dl_b200.models import resnet50
     torch.manual_seed(0)
