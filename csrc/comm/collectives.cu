@@ -35,6 +35,7 @@
 #include "../common/ptx.cuh"
 #include "../../include/dtdl_b200.h"
 
+#include <stdlib.h>
 #include <string.h>
 
 namespace dtdl {
@@ -306,10 +307,15 @@ __device__ __forceinline__ void multimem_st_f4(float* mc, float4 v) {
 // slice's parameters / optimizer state are read and written locally, as in two-shot.  The order
 // in which the switch adds the W values is fixed by the hardware, not by rank; results are
 // still identical on every rank because every rank receives the same stored value.
-__global__ void __launch_bounds__(512)
+//
+// kUnroll x 16 bytes of in-switch reductions are in flight per thread before the first is consumed;
+// (kUnroll, kThreads) is picked at run time from the measured sweep (DTDL_NVLS_UNROLL /
+// DTDL_NVLS_THREADS override): 512 threads x 4 keeps the register count under the 128 that a
+// 512-thread CTA allows, 256 x 8 trades occupancy for deeper per-thread queues.
+template <int kUnroll, int kThreads>
+__global__ void __launch_bounds__(kThreads)
 nvls_reduce_kernel(const CommDev c, const ReduceArgs a, TraceSlot* slot) {
-  constexpr int kUnroll = 4;
-  trace_enter(slot, TR_REDUCE, a.n * 4);
+  trace_enter(slot, TR_NVLS_REDUCE, a.n * 4);
   const int W = c.world;
   const long long n4 = a.n / 4;
   const long long per = (n4 + W - 1) / W;
@@ -405,6 +411,23 @@ local_update_kernel(float* __restrict__ param, const float* __restrict__ grad,
     }
     reinterpret_cast<float4*>(mom)[i] = m;
     reinterpret_cast<float4*>(param)[i] = p;
+  }
+}
+
+static void launch_nvls_reduce(const CommDev& d, const ReduceArgs& a, int grid, cudaStream_t stream,
+                               TraceSlot* slot) {
+  static const int unroll = getenv("DTDL_NVLS_UNROLL") ? atoi(getenv("DTDL_NVLS_UNROLL")) : 4;
+  static const int threads = getenv("DTDL_NVLS_THREADS") ? atoi(getenv("DTDL_NVLS_THREADS")) : 512;
+  if (threads == 256) {
+    if (unroll >= 8)
+      nvls_reduce_kernel<8, 256><<<grid * 2, 256, 0, stream>>>(d, a, slot);
+    else
+      nvls_reduce_kernel<4, 256><<<grid * 2, 256, 0, stream>>>(d, a, slot);
+  } else {
+    if (unroll >= 8)
+      nvls_reduce_kernel<8, 512><<<grid, 512, 0, stream>>>(d, a, slot);
+    else
+      nvls_reduce_kernel<4, 512><<<grid, 512, 0, stream>>>(d, a, slot);
   }
 }
 
@@ -680,7 +703,7 @@ extern "C" int dtdl_comm_nvls_allreduce(void* handle, void* mc_src, void* mc_dst
   a.scale = scale;
   const int grid = comm_grid(n / 4, h->d.world, 1, max_blocks > 0 ? max_blocks : 64);
   if (sync_before(h, STREAM(stream))) return 1;
-  nvls_reduce_kernel<<<grid, 512, 0, STREAM(stream)>>>(h->d, a, next_slot(h));
+  launch_nvls_reduce(h->d, a, grid, STREAM(stream), next_slot(h));
   DTDL_CHECK_CUDA(cudaGetLastError());
   return sync_after(h, STREAM(stream));
 }
@@ -708,7 +731,7 @@ extern "C" int dtdl_comm_nvls_reduce_update(void* handle, void* mc_grads, void* 
   a.scale = 1.f;
   const int grid = comm_grid(n / 4, h->d.world, 1, max_blocks > 0 ? max_blocks : 64);
   if (sync_before(h, STREAM(stream))) return 1;
-  nvls_reduce_kernel<<<grid, 512, 0, STREAM(stream)>>>(h->d, a, next_slot(h));
+  launch_nvls_reduce(h->d, a, grid, STREAM(stream), next_slot(h));
   DTDL_CHECK_CUDA(cudaGetLastError());
   return sync_after(h, STREAM(stream));
 }
