@@ -18,6 +18,8 @@
 #include "../common/ptx.cuh"
 #include "../../include/dtdl_b200.h"
 
+#include <stdlib.h>
+
 namespace dtdl {
 
 // V channels of one pixel as floats; V = 8 <-> a uint4 of bf16, V = 4 <-> a uint4 of fp32.
@@ -477,6 +479,198 @@ __global__ void bn_bwd_apply_kernel(const BnBwdArgs a) {
       for (int k = 0; k < V; ++k) o.v[k] += e.v[k];
     }
     a.dx[i] = packv<V>(o);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// BN backward in ONE kernel (both passes above): the two per-channel sums need every pixel before
+// any dx can be written, so the two-kernel form reads dy, x (and the ReLU mask y) twice.  Here each
+// CTA keeps its slice of the masked gradient and of x in shared memory across a grid-wide barrier:
+//   phase 1  load dy, x, y once; store g = dy*[y>0] and x into shared memory; per-channel partial
+//            sums -> block reduction -> atomics into sums2
+//   barrier  all CTAs (cooperative launch: the grid is co-resident)
+//   phase 2  coefficients from sums2; dx (+ add_in) and dres from the shared-memory copies
+// Per layer that is 3 tensor reads + 1 write instead of 6 + 1, and one launch instead of two.  The
+// aggregate shared memory of the GPU (148 x ~200 KB) bounds the layer size; larger layers take the
+// two-kernel path.  Covers K-O6 / K-O7 of SURVEY.md 2.5 (autograd of pytorch/model.py:27,30,33,34).
+// ---------------------------------------------------------------------------
+struct GridBarrier {
+  unsigned int count;
+  unsigned int generation;
+};
+
+__device__ __forceinline__ void grid_barrier(GridBarrier* b) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned int gen = *reinterpret_cast<volatile unsigned int*>(&b->generation);
+    if (atomicAdd(&b->count, 1u) == gridDim.x - 1) {
+      b->count = 0;
+      __threadfence();
+      atomicAdd(&b->generation, 1u);
+    } else {
+      long long t0 = clock64();
+      while (*reinterpret_cast<volatile unsigned int*>(&b->generation) == gen) {
+        __nanosleep(32);
+        if (clock64() - t0 > DTDL_SPIN_TIMEOUT_CYCLES) {
+          printf("[dtdl] grid barrier timed out: block %d of %d\n", blockIdx.x, gridDim.x);
+          __trap();
+        }
+      }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+template <int V>
+__global__ void __launch_bounds__(512, 1)
+bn_bwd_fused_kernel(const BnBwdArgs a, float* sums2, GridBarrier* bar, int rows_per_cta, int keep_x) {
+  extern __shared__ uint4 fsm[];
+  const int G = a.G, Cp = G * V;
+  const int rows = blockDim.x / G;                 // pixel rows handled per pass by this CTA
+  const int g = threadIdx.x % G, rrow = threadIdx.x / G;
+  uint4* s_g = fsm;                                // [rows_per_cta][G] masked gradient
+  uint4* s_x = fsm + (size_t)rows_per_cta * G;     // [rows_per_cta][G] BN input (keep_x only:
+                                                   // wide fp32 layers re-read x in phase 2 instead)
+  float* s_f = reinterpret_cast<float*>(fsm + (size_t)(keep_x ? 2 : 1) * rows_per_cta * G);   // reduction / coefficients
+  const long long p0 = (long long)blockIdx.x * rows_per_cta;
+  long long p1 = p0 + rows_per_cta;
+  if (p1 > a.P) p1 = a.P;
+
+  float m[V], rs[V], s1[V], s2[V];
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    const int c = g * V + k;
+    m[k] = c < a.C ? a.mean[c] : 0.f;
+    rs[k] = c < a.C ? a.rstd[c] : 0.f;
+    s1[k] = s2[k] = 0.f;
+  }
+  // One CTA per SM leaves few warps to hide the load latency, so every thread keeps kU rows' worth
+  // of loads in flight before it consumes the first.
+  constexpr int kU = 4;
+  if (rrow < rows) {
+    for (long long pb = p0 + rrow; pb < p1; pb += (long long)rows * kU) {
+      uint4 dr[kU], xr[kU], yr[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long p = pb + (long long)u * rows;
+        if (p < p1) {
+          dr[u] = a.dy[p * G + g];
+          xr[u] = a.x[p * G + g];
+          if (a.relu) yr[u] = a.y[p * G + g];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long p = pb + (long long)u * rows;
+        if (p < p1) {
+          FV<V> d = unpackv<V>(dr[u]);
+          const FV<V> xv = unpackv<V>(xr[u]);
+          if (a.relu) {
+            const FV<V> yv = unpackv<V>(yr[u]);
+#pragma unroll
+            for (int k = 0; k < V; ++k)
+              if (!(yv.v[k] > 0.f)) d.v[k] = 0.f;
+          }
+          const size_t li = (size_t)(p - p0) * G + g;
+          s_g[li] = packv<V>(d);
+          if (keep_x) s_x[li] = xr[u];
+#pragma unroll
+          for (int k = 0; k < V; ++k) {
+            s1[k] += d.v[k];
+            s2[k] += d.v[k] * (xv.v[k] - m[k]) * rs[k];
+          }
+        }
+      }
+    }
+  }
+  float* mine = s_f + (size_t)threadIdx.x * (2 * V);
+#pragma unroll
+  for (int k = 0; k < V; ++k) {
+    mine[k] = s1[k];
+    mine[V + k] = s2[k];
+  }
+  __syncthreads();
+  for (int o = threadIdx.x; o < G * 2 * V; o += blockDim.x) {
+    const int og = o / (2 * V), ok = o % (2 * V);
+    float acc = 0.f;
+    for (int rr = 0; rr < rows; ++rr) acc += s_f[((size_t)rr * G + og) * (2 * V) + ok];
+    if (ok < V)
+      atomicAdd(&sums2[og * V + ok], acc);
+    else
+      atomicAdd(&sums2[Cp + og * V + (ok - V)], acc);
+  }
+  grid_barrier(bar);
+
+  // coefficients (same arithmetic as bn_bwd_apply_kernel)
+  float* k1 = s_f;
+  float* k2 = s_f + Cp;
+  float* k3 = s_f + 2 * Cp;
+  for (int c = threadIdx.x; c < Cp; c += blockDim.x) {
+    if (c < a.C) {
+      const float sg = __ldcg(sums2 + c), sgx = __ldcg(sums2 + Cp + c);
+      k1[c] = a.gamma[c] * a.rstd[c];
+      k2[c] = sg / (float)a.P;
+      k3[c] = sgx / (float)a.P;
+      if (blockIdx.x == 0) {
+        if (a.accumulate) {
+          a.dgamma[c] += sgx;
+          a.dbeta[c] += sg;
+        } else {
+          a.dgamma[c] = sgx;
+          a.dbeta[c] = sg;
+        }
+      }
+    } else {
+      k1[c] = k2[c] = k3[c] = 0.f;
+    }
+  }
+  if (blockIdx.x == 0 && a.zero_buf != nullptr)
+    for (int i = threadIdx.x; i < a.zero_n; i += blockDim.x) a.zero_buf[i] = 0.f;
+  __syncthreads();
+  if (rrow < rows) {
+    float c1[V], c2[V], c3[V];
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      c1[k] = k1[g * V + k];
+      c2[k] = k2[g * V + k];
+      c3[k] = k3[g * V + k];
+    }
+    for (long long pb = p0 + rrow; pb < p1; pb += (long long)rows * kU) {
+      uint4 xr[kU], er[kU];
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long p = pb + (long long)u * rows;
+        if (p < p1) {
+          if (!keep_x) xr[u] = a.x[p * G + g];
+          if (a.add_in != nullptr) er[u] = a.add_in[p * G + g];
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kU; ++u) {
+        const long long p = pb + (long long)u * rows;
+        if (p < p1) {
+          const size_t li = (size_t)(p - p0) * G + g;
+          const uint4 gr = s_g[li];
+          const FV<V> d = unpackv<V>(gr);
+          const FV<V> xv = unpackv<V>(keep_x ? s_x[li] : xr[u]);
+          if (a.dres != nullptr && g < a.Gres) a.dres[p * a.Gres + g] = gr;
+          FV<V> o;
+#pragma unroll
+          for (int k = 0; k < V; ++k) {
+            const float xhat = (xv.v[k] - m[k]) * rs[k];
+            o.v[k] = c1[k] * (d.v[k] - c2[k] - xhat * c3[k]);
+          }
+          if (a.add_in != nullptr) {
+            const FV<V> e = unpackv<V>(er[u]);
+#pragma unroll
+            for (int k = 0; k < V; ++k) o.v[k] += e.v[k];
+          }
+          a.dx[p * G + g] = packv<V>(o);
+        }
+      }
+    }
   }
 }
 
@@ -1060,6 +1254,91 @@ extern "C" int dtdl_bn_bwd_add(const void* dy, const void* x, const void* y, con
   const long long total = P * G;
   LAUNCH_ACT(act, bn_bwd_apply_kernel, grid_for(total, 256 * 4, kMaxBlocks), 256, 5 * Cp * sizeof(float),
              stream, a);
+  return 0;
+}
+
+// Launch plan of the one-kernel BatchNorm backward; false when the layer does not fit.
+static bool bn_fused_plan(long long P, int Cp, int act, int* grid, int* block, int* rows_per_cta, size_t* smem,
+                          int* keep_x) {
+  static const bool off = getenv("DTDL_BN_FUSED_BWD") != nullptr && atoi(getenv("DTDL_BN_FUSED_BWD")) == 0;
+  if (off) return false;
+  const int V = vec_of(act);
+  const int G = Cp / V;
+  if (G < 1 || G > 512 || P < 1) return false;
+  const int sms = sm_count();
+  *block = G * (512 / G);
+  *rows_per_cta = (int)((P + sms - 1) / sms);
+  *grid = (int)((P + *rows_per_cta - 1) / *rows_per_cta);
+  const size_t fl = (size_t)(*block) * 2 * V > (size_t)3 * Cp ? (size_t)(*block) * 2 * V : (size_t)3 * Cp;
+  // both tiles resident when they fit; otherwise only the masked gradient (x is read again in phase 2)
+  *keep_x = 1;
+  *smem = (size_t)2 * (*rows_per_cta) * G * 16 + fl * sizeof(float);
+  if (*smem <= 216 * 1024) return true;
+  *keep_x = 0;
+  *smem = (size_t)(*rows_per_cta) * G * 16 + fl * sizeof(float);
+  return *smem <= 216 * 1024;
+}
+
+extern "C" int dtdl_bn_bwd_fused_fits(long long P, int Cp, int act) {
+  int grid, block, rows, keep_x;
+  size_t smem;
+  return (act == kActBf16 || act == kActF32) && Cp % 8 == 0 &&
+                 bn_fused_plan(P, Cp, act, &grid, &block, &rows, &smem, &keep_x)
+             ? 1
+             : 0;
+}
+
+// Same contract as dtdl_bn_bwd_add; `barrier` = 8 zero-initialised bytes of device memory owned by
+// the caller (the grid barrier's counter and generation; one per concurrently running call).
+extern "C" int dtdl_bn_bwd_fused(const void* dy, const void* x, const void* y, const float* save_mean,
+                                 const float* save_rstd, const float* gamma, float* sums2, void* dx,
+                                 void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
+                                 long long P, int C, int Cp, int relu, float* zero_buf, int zero_n,
+                                 const void* add_in, void* barrier, int act, void* stream) {
+  DTDL_ACT_OK(act);
+  const int V = vec_of(act);
+  DTDL_REQUIRE(Cp % 8 == 0 && Cres_p % 8 == 0 && Cres_p <= Cp, "bad channel padding");
+  DTDL_REQUIRE(!relu || y != nullptr, "relu backward needs the saved output");
+  DTDL_REQUIRE(barrier != nullptr, "the fused BatchNorm backward needs its barrier words");
+  int grid, block, rows_per_cta, keep_x;
+  size_t smem;
+  DTDL_REQUIRE(bn_fused_plan(P, Cp, act, &grid, &block, &rows_per_cta, &smem, &keep_x),
+               "layer too large for the one-kernel BatchNorm backward (see dtdl_bn_bwd_fused_fits)");
+  static bool attr[64] = {false};
+  int dev = 0;
+  DTDL_CHECK_CUDA(cudaGetDevice(&dev));
+  if (!attr[dev & 63]) {
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(bn_bwd_fused_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    DTDL_CHECK_CUDA(cudaFuncSetAttribute(bn_bwd_fused_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr[dev & 63] = true;
+  }
+  BnBwdArgs a;
+  a.dy = reinterpret_cast<const uint4*>(dy);
+  a.x = reinterpret_cast<const uint4*>(x);
+  a.y = reinterpret_cast<const uint4*>(y);
+  a.mean = save_mean;
+  a.rstd = save_rstd;
+  a.gamma = gamma;
+  a.sums2 = sums2;
+  a.dx = reinterpret_cast<uint4*>(dx);
+  a.dres = reinterpret_cast<uint4*>(dres);
+  a.Gres = Cres_p / V;
+  a.dgamma = dgamma;
+  a.dbeta = dbeta;
+  a.accumulate = accumulate;
+  a.P = P;
+  a.C = C;
+  a.G = Cp / V;
+  a.relu = relu;
+  a.zero_buf = zero_buf;
+  a.zero_n = zero_n;
+  a.add_in = reinterpret_cast<const uint4*>(add_in);
+  GridBarrier* bar = reinterpret_cast<GridBarrier*>(barrier);
+  void* args[] = {&a, &sums2, &bar, &rows_per_cta, &keep_x};
+  const void* fn = act == kActF32 ? reinterpret_cast<const void*>(bn_bwd_fused_kernel<4>)
+                                  : reinterpret_cast<const void*>(bn_bwd_fused_kernel<8>);
+  // cooperative launch: every CTA of the grid is resident at once, which the grid barrier needs
+  DTDL_CHECK_CUDA(cudaLaunchCooperativeKernel(fn, dim3(grid), dim3(block), args, smem, STREAM(stream)));
   return 0;
 }
 

@@ -103,7 +103,7 @@ def check(rc):
 _LAUNCHES = {"conv_fprop": 1, "conv_fprop_stats": 1, "conv_dgrad_s2": 4, "comm_nvls_allreduce": 1,
              "comm_nvls_reduce_update": 1, "comm_nvls_broadcast": 1, "conv_wgrad": 2, "pack_weights": 1,
              "nchw_to_nhwc": 1, "nchw_to_s2d": 1, "bn_stats": 1, "bn_apply": 1, "bn_apply_stats": 1, "bn_bwd": 2,
-             "bn_bwd_add": 2, "relu_bwd": 1, "add": 1, "add_prefix": 1, "pool_fwd": 1, "pool_bwd": 1,
+             "bn_bwd_add": 2, "bn_bwd_fused": 1, "relu_bwd": 1, "add": 1, "add_prefix": 1, "pool_fwd": 1, "pool_bwd": 1,
              "subsample2": 1, "gap_fwd": 1, "gap_bwd": 1, "softmax_ce": 1, "colsum": 1, "pad_cast": 1,
              "unpad_cast": 1, "linear_f32_fwd": 1, "linear_f32_bwd": 2, "comm_barrier": 1, "comm_allreduce": 1,
              "comm_reduce_update": 1, "comm_broadcast": 1, "comm_allgather": 1, "local_update": 1}

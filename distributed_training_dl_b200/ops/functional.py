@@ -508,10 +508,22 @@ class _BatchNorm(torch.autograd.Function):
         dres = None
         if ctx.Cres_p and ctx.needs_input_grad[3]:
             dres = torch.empty((N, H, W, ctx.Cres_p), dtype=x.dtype, device=x.device)
-        nv.call("bn_bwd_add", nv.ptr(dy), nv.ptr(x), nv.ptr(y), nv.ptr(save[0]), nv.ptr(save[1]),
-                nv.ptr(gamma), stat[2 * Cp:].data_ptr(), nv.ptr(dx), nv.ptr(dres), ctx.Cres_p,
-                nv.ptr(gg), nv.ptr(gb), 1 if (acc_g or acc_b) else 0, P, mod.num_features, Cp,
-                1 if ctx.relu else 0, nv.ptr(stat), 2 * Cp, nv.ptr(add_in), act_of(x), st)
+        act = act_of(x)
+        fits = mod._fused_bwd_fits.get((P, Cp, act))
+        if fits is None:
+            fits = mod._fused_bwd_fits[(P, Cp, act)] = bool(nv.lib().dtdl_bn_bwd_fused_fits(P, Cp, act))
+        if fits:
+            # one cooperative kernel: dy / x / y cross L2 -> SM once, not twice (csrc/ops/nn_ops.cu)
+            nv.call("bn_bwd_fused", nv.ptr(dy), nv.ptr(x), nv.ptr(y), nv.ptr(save[0]), nv.ptr(save[1]),
+                    nv.ptr(gamma), stat[2 * Cp:].data_ptr(), nv.ptr(dx), nv.ptr(dres), ctx.Cres_p,
+                    nv.ptr(gg), nv.ptr(gb), 1 if (acc_g or acc_b) else 0, P, mod.num_features, Cp,
+                    1 if ctx.relu else 0, nv.ptr(stat), 2 * Cp, nv.ptr(add_in),
+                    nv.ptr(mod._grid_barrier(x.device)), act, st)
+        else:
+            nv.call("bn_bwd_add", nv.ptr(dy), nv.ptr(x), nv.ptr(y), nv.ptr(save[0]), nv.ptr(save[1]),
+                    nv.ptr(gamma), stat[2 * Cp:].data_ptr(), nv.ptr(dx), nv.ptr(dres), ctx.Cres_p,
+                    nv.ptr(gg), nv.ptr(gb), 1 if (acc_g or acc_b) else 0, P, mod.num_features, Cp,
+                    1 if ctx.relu else 0, nv.ptr(stat), 2 * Cp, nv.ptr(add_in), act, st)
         mod._fwd_dirty = False
         _grad_ready(gamma)
         _grad_ready(beta)

@@ -158,6 +158,13 @@ class BatchNorm2d(nn.BatchNorm2d):
         self._stat = None
         self._fwd_dirty = False
         self._stats_from_producer = False   # set by the kernel that sums our input for us
+        self._fused_bwd_fits = {}           # (P, Cp, act) -> the one-kernel backward applies
+        self._bar = None                    # its grid-barrier words (device memory, zero-initialised)
+
+    def _grid_barrier(self, device):
+        if self._bar is None or self._bar.device != device:
+            self._bar = torch.zeros(2, dtype=torch.int32, device=device)
+        return self._bar
 
     def _stat_buffer(self, device, Cp):
         if self._stat is None or self._stat.device != device or self._stat.numel() != 4 * Cp:

@@ -122,6 +122,16 @@ int dtdl_bn_bwd_add(const void* dy, const void* x, const void* y, const float* s
                 void* dx, void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
                 long long P, int C, int Cp, int relu, float* zero_buf, int zero_n, const void* add_in,
                 int act, void* stream);
+/* dtdl_bn_bwd_add as ONE cooperative kernel: each CTA keeps its slice of the masked gradient and of x in
+ * shared memory across a grid barrier, so dy / x / y are read once instead of twice.  Only for layers
+ * whose dy + x fit the GPU's aggregate shared memory (dtdl_bn_bwd_fused_fits: 1 / 0).  `barrier` = 8
+ * zeroed bytes of device memory owned by the caller, not shared with a concurrently running call. */
+int dtdl_bn_bwd_fused_fits(long long P, int Cp, int act);
+int dtdl_bn_bwd_fused(const void* dy, const void* x, const void* y, const float* save_mean,
+                const float* save_rstd, const float* gamma, float* sums2 /* [2*Cp], zeroed */,
+                void* dx, void* dres, int Cres_p, float* dgamma, float* dbeta, int accumulate,
+                long long P, int C, int Cp, int relu, float* zero_buf, int zero_n, const void* add_in,
+                void* barrier, int act, void* stream);
 int dtdl_relu_bwd(const void* dy, const void* y, void* dx, long long n_elems, int act, void* stream);
 int dtdl_add(const void* a, const void* b, void* out, long long n_elems, int act, void* stream);
 int dtdl_add_prefix(void* a, const void* b, long long P, int Ca_p, int Cb_p, int act, void* stream);

@@ -332,3 +332,52 @@ def test_resnet50_whole_model():
         ga = dict(cpu.named_parameters())[n].grad.flatten().double()
         gb = dict(gpu.named_parameters())[n].grad.cpu().flatten().double()
         assert torch.dot(ga, gb) / (ga.norm() * gb.norm()) > 0.97, n
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("P,C,Cres,relu", [(8192, 21, 16, True), (65536, 61, 0, True), (4096, 271, 271, False), (300, 8, 8, True)])
+def test_bn_backward_one_kernel_equals_two_kernels(P, C, Cres, relu, dtype):
+    """dtdl_bn_bwd_fused (cooperative, tiles kept in shared memory across a grid barrier) against
+    dtdl_bn_bwd_add (reduce kernel + apply kernel) on the same inputs, twice in a row (the barrier
+    words and the zeroed sums are reused between calls)."""
+    from distributed_training_dl_b200 import _native as nv
+    from distributed_training_dl_b200.ops import functional as fn
+    act = fn.act_of(dtype)
+    Cp, Cres_p = fn.pad8(C), fn.pad8(Cres) if Cres else 0
+    assert nv.lib().dtdl_bn_bwd_fused_fits(P, Cp, act) == 1      # (65536, 64ch, fp32): gradient-only residency
+    assert nv.lib().dtdl_bn_bwd_fused_fits(1 << 22, 256, act) == 0  # too large for the GPU's shared memory
+    torch.manual_seed(0)
+    st = nv.stream_ptr()
+    bar = torch.zeros(2, dtype=torch.int32, device="cuda")
+    for rep in range(2):
+        def rnd(c, cp):
+            t = torch.zeros(P, cp, device="cuda")
+            t[:, :c] = torch.randn(P, c, device="cuda")
+            return t.to(dtype)
+        dy, x, y, add_in = rnd(C, Cp), rnd(C, Cp), rnd(C, Cp), rnd(C, Cp)
+        mean, rstd = torch.randn(Cp, device="cuda") * 0.1, torch.rand(Cp, device="cuda") + 0.5
+        gamma = torch.rand(C, device="cuda") + 0.5
+        outs = []
+        for fused in (False, True):
+            sums2 = torch.zeros(2 * Cp, device="cuda")
+            dx = torch.full((P, Cp), float("nan"), device="cuda").to(dtype)
+            dres = torch.full((P, Cres_p), float("nan"), device="cuda").to(dtype) if Cres else None
+            dg, db = torch.zeros(C, device="cuda"), torch.zeros(C, device="cuda")
+            zero = torch.ones(16, device="cuda")
+            args = [nv.ptr(dy), nv.ptr(x), nv.ptr(y), nv.ptr(mean), nv.ptr(rstd), nv.ptr(gamma), nv.ptr(sums2),
+                    nv.ptr(dx), nv.ptr(dres), Cres_p, nv.ptr(dg), nv.ptr(db), 0, P, C, Cp, 1 if relu else 0,
+                    nv.ptr(zero), 16, nv.ptr(add_in)]
+            if fused:
+                nv.call("bn_bwd_fused", *args, nv.ptr(bar), act, st)
+            else:
+                nv.call("bn_bwd_add", *args, act, st)
+            torch.cuda.synchronize()
+            assert float(zero.abs().sum()) == 0
+            outs.append((dx.float(), dres.float() if Cres else None, dg, db))
+        (dx0, dr0, dg0, db0), (dx1, dr1, dg1, db1) = outs
+        assert torch.isfinite(dx1).all()
+        tol = 2e-2 if dtype == torch.bfloat16 else 1e-4       # sums are float atomics in both: order differs
+        assert _rel_err(dx1, dx0) < tol
+        assert _rel_err(dg1, dg0) < 1e-3 and _rel_err(db1, db0) < 1e-3
+        if Cres:
+            assert torch.equal(dr1, dr0)
