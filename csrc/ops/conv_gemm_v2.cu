@@ -24,6 +24,8 @@
 #include "../../include/dtdl_b200.h"
 #include "epilogue.cuh"
 
+#include <stdlib.h>
+
 namespace dtdl {
 
 struct ConvV2Args {
@@ -207,9 +209,13 @@ int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, 
   a.BH = BH;
   const int Np16 = (Cout_p + 15) / 16 * 16;
   // N tiling: a single tile when it fits 192 columns (two accumulators <= 384 TMEM columns)
-  int n_tiles = (Np16 + 191) / 192;
+  // tuning overrides for measurements (tools/bench_kernels.py): widest N tile, sub-tiles per CTA, stages
+  static const int env_ntile = getenv("DTDL_V2_NTILE") ? atoi(getenv("DTDL_V2_NTILE")) : 192;
+  static const int env_ms = getenv("DTDL_V2_MS") ? atoi(getenv("DTDL_V2_MS")) : 2;
+  static const int env_stages = getenv("DTDL_V2_STAGES") ? atoi(getenv("DTDL_V2_STAGES")) : 6;
+  int n_tiles = (Np16 + env_ntile - 1) / env_ntile;
   int n_tile = ((Np16 + n_tiles - 1) / n_tiles + 15) / 16 * 16;
-  int MS = (Ho >= 2 * BH) ? 2 : 1;
+  int MS = (Ho >= 2 * BH && env_ms >= 2) ? 2 : 1;
   a.b_box_bytes = (n_tile * 128 + 1023) / 1024 * 1024;
   for (;;) {
     a.halo_rows = (MS * BH + KH - 1) * BW;
@@ -244,7 +250,7 @@ int conv_fprop_v2(const void* x, const void* wpack, void* y, const float* bias, 
   const long long ctas = (long long)N * a.tiles_h * n_tiles;
   const bool two_per_sm = 2 * a.stage_bytes <= 108 * 1024 && a.tmem_cols <= 256 && ctas > sm_count();
   int stages = ((two_per_sm ? 108 : 220) * 1024) / a.stage_bytes;
-  if (stages > 6) stages = 6;
+  if (stages > env_stages) stages = env_stages;
   const int n_groups = KW * a.chunks;
   if (stages > n_groups) stages = n_groups < 2 ? 2 : n_groups;
   a.stages = stages;
