@@ -340,6 +340,126 @@ nvls_reduce_kernel(const CommDev c, const ReduceArgs a, TraceSlot* slot) {
   trace_exit(slot);
 }
 
+// ---- bf16 gradient transport -------------------------------------------------------------------
+// Option of the fused reducer (wrap(..., grad_dtype="bf16")): the bucket's fp32 gradients are cast to
+// bf16 into a second symmetric arena (cast_f32_bf16_kernel, on the communication stream), and the
+// reduce kernels below move HALF the bytes over NVLink: every 16-byte peer / multicast load carries 8
+// gradients, the sum is accumulated in fp32 (multimem: .acc::f32), and the fp32 epilogue -- 1/W,
+// weight decay, SGD / Adam, fp32 parameter store to every rank -- is the same as above.  This is the
+// "fp32/bf16 cast fused with the collective and the update" of the north star; the reference's DDP
+// moves fp32 gradients (pytorch/distributed_data_parallel.py:132), so fp32 stays the default.
+__global__ void __launch_bounds__(256)
+cast_f32_bf16_kernel(const float4* __restrict__ src, uint2* __restrict__ dst, long long n4) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += stride) {
+    const float4 v = src[i];
+    __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+    dst[i] = make_uint2(*reinterpret_cast<uint32_t*>(&a), *reinterpret_cast<uint32_t*>(&b));
+  }
+}
+
+struct F8s {
+  float4 lo, hi;
+};
+__device__ __forceinline__ F8s bf16x8_to_f32(uint4 u) {
+  F8s r;
+  const __nv_bfloat162* p = reinterpret_cast<const __nv_bfloat162*>(&u);
+  const float2 a = __bfloat1622float2(p[0]), b = __bfloat1622float2(p[1]), c = __bfloat1622float2(p[2]),
+               d = __bfloat1622float2(p[3]);
+  r.lo = make_float4(a.x, a.y, b.x, b.y);
+  r.hi = make_float4(c.x, c.y, d.x, d.y);
+  return r;
+}
+__device__ __forceinline__ uint4 ld_nc_u4(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+
+// Two-shot over peer pointers, bf16 gradients (grads.p[r] = rank r's bf16 bucket).  a.n is a multiple of 8.
+template <int WT>
+__global__ void __launch_bounds__(512)
+reduce16_kernel(const CommDev c, const ReduceArgs a, TraceSlot* slot) {
+  trace_enter(slot, TR_REDUCE, a.n * 2);
+  const int W = WT ? WT : c.world;
+  long long begin8 = 0, end8 = a.n / 8;
+  if (W > 1) {
+    const long long per = (end8 + W - 1) / W;
+    begin8 = per * c.rank;
+    end8 = begin8 + per < end8 ? begin8 + per : end8;
+    if (begin8 > end8) begin8 = end8;
+  }
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = begin8 + blockIdx.x * (long long)blockDim.x + threadIdx.x; i < end8; i += stride) {
+    uint4 raw[WT ? WT : kMaxWorld];
+#pragma unroll
+    for (int r = 0; r < (WT ? WT : kMaxWorld); ++r)
+      if (r < W) raw[r] = ld_nc_u4(reinterpret_cast<const uint4*>(a.grads.p[r]) + i);
+    F8s s = bf16x8_to_f32(raw[0]);
+#pragma unroll
+    for (int r = 1; r < (WT ? WT : kMaxWorld); ++r) {
+      if (r < W) {
+        const F8s t = bf16x8_to_f32(raw[r]);
+        s.lo = f4_add(s.lo, t.lo);
+        s.hi = f4_add(s.hi, t.hi);
+      }
+    }
+    const float4 o0 = reduce_epilogue(a, 2 * i, s.lo), o1 = reduce_epilogue(a, 2 * i + 1, s.hi);
+#pragma unroll
+    for (int r = 0; r < (WT ? WT : kMaxWorld); ++r) {
+      if (r < W) {
+        reinterpret_cast<float4*>(a.dst.p[r])[2 * i] = o0;
+        reinterpret_cast<float4*>(a.dst.p[r])[2 * i + 1] = o1;
+      }
+    }
+  }
+  trace_exit(slot);
+}
+
+// Multicast form: one in-switch bf16 reduction (fp32 accumulate) per 16 bytes = 8 gradients.
+__global__ void __launch_bounds__(512)
+nvls_reduce16_kernel(const CommDev c, const ReduceArgs a, TraceSlot* slot) {
+  constexpr int kUnroll = 4;
+  trace_enter(slot, TR_NVLS_REDUCE, a.n * 2);
+  const int W = c.world;
+  const long long n8 = a.n / 8;
+  const long long per = (n8 + W - 1) / W;
+  long long begin8 = per * c.rank;
+  const long long end8 = begin8 + per < n8 ? begin8 + per : n8;
+  if (begin8 > end8) begin8 = end8;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const char* mc = reinterpret_cast<const char*>(a.mc_grads);
+  for (long long i0 = begin8 + blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 < end8;
+       i0 += stride * kUnroll) {
+    uint4 raw[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < end8) raw[u] = multimem_ld_reduce_bf16x8(mc + 16 * i);
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const long long i = i0 + u * stride;
+      if (i < end8) {
+        const F8s s = bf16x8_to_f32(raw[u]);
+        multimem_st_f4(a.mc_dst + 8 * i, reduce_epilogue(a, 2 * i, s.lo));
+        multimem_st_f4(a.mc_dst + 8 * i + 4, reduce_epilogue(a, 2 * i + 1, s.hi));
+      }
+    }
+  }
+  trace_exit(slot);
+}
+
 // The root pushes its copy once; the switch delivers it to every rank (the root included).
 __global__ void __launch_bounds__(512)
 nvls_broadcast_kernel(const CommDev c, const float* local, float* mc, long long n16, int root,
@@ -750,6 +870,86 @@ extern "C" int dtdl_comm_nvls_broadcast(void* handle, void* local, void* mc, lon
   nvls_broadcast_kernel<<<(int)g, 512, 0, STREAM(stream)>>>(
       h->d, reinterpret_cast<const float*>(reinterpret_cast<char*>(local) + offset_bytes),
       reinterpret_cast<float*>(reinterpret_cast<char*>(mc) + offset_bytes), n16, root, next_slot(h));
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return sync_after(h, STREAM(stream));
+}
+
+// ---- bf16 gradient transport: entry points ------------------------------------------------------
+extern "C" int dtdl_cast_f32_bf16(const float* src, void* dst, long long n, void* stream) {
+  DTDL_REQUIRE(n % 4 == 0, "element count must be a multiple of 4");
+  long long g = (n / 4 + 1023) / 1024;
+  if (g > 148 * 4) g = 148 * 4;
+  if (g < 1) g = 1;
+  cast_f32_bf16_kernel<<<(int)g, 256, 0, STREAM(stream)>>>(reinterpret_cast<const float4*>(src),
+                                                           reinterpret_cast<uint2*>(dst), n / 4);
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+static void launch_reduce16(const CommDev& d, const ReduceArgs& a, int grid, cudaStream_t stream,
+                            TraceSlot* slot) {
+  switch (d.world) {
+    case 1: reduce16_kernel<1><<<grid, 512, 0, stream>>>(d, a, slot); break;
+    case 2: reduce16_kernel<2><<<grid, 512, 0, stream>>>(d, a, slot); break;
+    case 4: reduce16_kernel<4><<<grid, 512, 0, stream>>>(d, a, slot); break;
+    case 8: reduce16_kernel<8><<<grid, 512, 0, stream>>>(d, a, slot); break;
+    default: reduce16_kernel<0><<<grid, 512, 0, stream>>>(d, a, slot); break;
+  }
+}
+
+// dtdl_comm_reduce_update with bf16 gradient buckets: grads16[r] = rank r's bf16 gradient arena;
+// `offset_bytes` is the bucket's offset in the fp32 arenas (the bf16 arena is addressed at half of it).
+extern "C" int dtdl_comm_reduce_update16(void* handle, void* const* grads16, void* const* params,
+                                         float* mom, float* var, const float* hyper,
+                                         long long offset_bytes, long long n, int opt, int max_blocks,
+                                         void* stream) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  DTDL_REQUIRE(n % 8 == 0 && offset_bytes % 32 == 0, "bf16 buckets must be 8-element granular");
+  DTDL_REQUIRE(opt == OPT_SGD || opt == OPT_ADAM || opt == OPT_ADAM_KERAS, "unknown optimizer");
+  ReduceArgs a;
+  memset(&a, 0, sizeof(a));
+  DTDL_REQUIRE(!fill_peers(&a.grads, grads16, h->d.world, offset_bytes / 2), "missing peer pointer");
+  DTDL_REQUIRE(!fill_peers(&a.dst, params, h->d.world, offset_bytes), "missing peer pointer");
+  a.param = reinterpret_cast<float*>(a.dst.p[h->d.rank]);
+  a.mom = reinterpret_cast<float*>(reinterpret_cast<char*>(mom) + offset_bytes);
+  a.var = var ? reinterpret_cast<float*>(reinterpret_cast<char*>(var) + offset_bytes) : nullptr;
+  DTDL_REQUIRE(opt == OPT_SGD || a.var != nullptr, "Adam needs the second-moment arena");
+  a.hyper = hyper;
+  a.n = n;
+  a.opt = opt;
+  a.two_shot = 1;
+  a.scale = 1.f;
+  const int grid = comm_grid(n / 8, h->d.world, 1, max_blocks > 0 ? max_blocks : 64);
+  if (sync_before(h, STREAM(stream))) return 1;
+  launch_reduce16(h->d, a, grid, STREAM(stream), next_slot(h));
+  DTDL_CHECK_CUDA(cudaGetLastError());
+  return sync_after(h, STREAM(stream));
+}
+
+extern "C" int dtdl_comm_nvls_reduce_update16(void* handle, void* mc_grads16, void* mc_params, float* param,
+                                              float* mom, float* var, const float* hyper,
+                                              long long offset_bytes, long long n, int opt, int max_blocks,
+                                              void* stream) {
+  CommHost* h = reinterpret_cast<CommHost*>(handle);
+  DTDL_REQUIRE(n % 8 == 0 && offset_bytes % 32 == 0, "bf16 buckets must be 8-element granular");
+  DTDL_REQUIRE(opt == OPT_SGD || opt == OPT_ADAM || opt == OPT_ADAM_KERAS, "unknown optimizer");
+  DTDL_REQUIRE(mc_grads16 != nullptr && mc_params != nullptr, "buffer has no multicast mapping");
+  ReduceArgs a;
+  memset(&a, 0, sizeof(a));
+  a.mc_grads = reinterpret_cast<const float*>(reinterpret_cast<char*>(mc_grads16) + offset_bytes / 2);
+  a.mc_dst = reinterpret_cast<float*>(reinterpret_cast<char*>(mc_params) + offset_bytes);
+  a.param = reinterpret_cast<float*>(reinterpret_cast<char*>(param) + offset_bytes);
+  a.mom = reinterpret_cast<float*>(reinterpret_cast<char*>(mom) + offset_bytes);
+  a.var = var ? reinterpret_cast<float*>(reinterpret_cast<char*>(var) + offset_bytes) : nullptr;
+  DTDL_REQUIRE(opt == OPT_SGD || a.var != nullptr, "Adam needs the second-moment arena");
+  a.hyper = hyper;
+  a.n = n;
+  a.opt = opt;
+  a.two_shot = 1;
+  a.scale = 1.f;
+  const int grid = comm_grid(n / 8, h->d.world, 1, max_blocks > 0 ? max_blocks : 64);
+  if (sync_before(h, STREAM(stream))) return 1;
+  nvls_reduce16_kernel<<<grid, 512, 0, STREAM(stream)>>>(h->d, a, next_slot(h));
   DTDL_CHECK_CUDA(cudaGetLastError());
   return sync_after(h, STREAM(stream));
 }

@@ -17,7 +17,7 @@ from dataclasses import dataclass
 
 import torch
 
-ALIGN = 4  # elements: keeps every tensor 16-byte aligned inside the arena
+ALIGN = 8  # elements: every tensor 32-byte aligned in the fp32 arenas, 16-byte in a bf16 gradient arena
 
 
 @dataclass
@@ -117,6 +117,16 @@ class ParamArena:
                 else:
                     p._dtdl_fresh = True
                 p._dtdl_arena = self
+
+    def enable_bf16_grads(self):
+        """Second, bf16 gradient arena for the reducer's bf16 transport option (symmetric like the
+        fp32 one; the fp32 gradients stay where the kernels write them and are cast per bucket)."""
+        if getattr(self, "grad16_buf", None) is None:
+            if self.peer is None:
+                raise RuntimeError("bf16 gradient transport needs the peer-memory back end")
+            self.grad16_buf = self.peer.alloc(self.numel * 2, "grads16")
+            self.grad16_flat = self.grad16_buf.view(torch.bfloat16, 0, self.numel)
+        return self.grad16_buf
 
     def flat_view_like(self, flat, p):
         off = self.offsets[id(p)]

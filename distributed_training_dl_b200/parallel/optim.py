@@ -234,7 +234,7 @@ class _FusedBase(torch.optim.Optimizer):
                 if buf is None:
                     continue
                 for b in a0.buckets:
-                    if red.peer.choose_two_shot(b.numel * 4):
+                    if red.peer.choose_two_shot(b.numel * 4) or getattr(red, "grad_bf16", False):
                         red.peer.allgather(buf, b.offset * 4, b.numel * 4)
         if a0.device.type == "cuda":
             torch.cuda.synchronize(a0.device)

@@ -500,6 +500,21 @@ class PeerComm:
                 self._stream(stream))
         self._count_sync()
 
+    def reduce_update16(self, grads16: SymmBuffer, params: SymmBuffer, mom, var, hyper, offset_bytes: int,
+                        numel: int, opt: int, stream=None, max_blocks=None):
+        """``reduce_update`` with the gradients travelling as bf16 (``grads16`` = the bf16 gradient arena,
+        already filled by ``cast_f32_bf16``): half the NVLink bytes, fp32 accumulation and update.
+        Multicast variant when both buffers are bound to a multicast object, else two-shot."""
+        if self._nvls_ok(grads16, params, numel * 2):
+            nv.call("comm_nvls_reduce_update16", self.handle, ctypes.c_void_p(grads16.mc_ptr),
+                    ctypes.c_void_p(params.mc_ptr), ctypes.c_void_p(params.local_ptr), nv.ptr(mom), nv.ptr(var),
+                    nv.ptr(hyper), offset_bytes, numel, opt, max_blocks or self.max_blocks, self._stream(stream))
+        else:
+            nv.call("comm_reduce_update16", self.handle, grads16.ptr_array, params.ptr_array, nv.ptr(mom),
+                    nv.ptr(var), nv.ptr(hyper), offset_bytes, numel, opt, max_blocks or self.max_blocks,
+                    self._stream(stream))
+        self._count_sync()
+
     def broadcast(self, buf: SymmBuffer, offset_bytes: int, nbytes: int, root: int = 0, stream=None,
                   max_blocks=None):
         if self._nvls_ok(buf, buf, nbytes):

@@ -36,7 +36,8 @@ class Reducer:
     """Bucketed gradient reducer.  Buckets launch strictly in index order on every rank, so
     all ranks issue the same sequence of collectives whatever the local gradient order."""
 
-    def __init__(self, module, comm, bucket_cap_mb=25.0, first_bucket_mb=1.0, broadcast_buffers=True):
+    def __init__(self, module, comm, bucket_cap_mb=25.0, first_bucket_mb=1.0, broadcast_buffers=True,
+                 grad_dtype="fp32"):
         # tuning overrides for measurements (tools/sweep_2gpu.sh): bucket sizes, buffer broadcast
         bucket_cap_mb = float(os.environ.get("DTDL_BUCKET_MB", bucket_cap_mb))
         first_bucket_mb = float(os.environ.get("DTDL_FIRST_BUCKET_MB", first_bucket_mb))
@@ -66,6 +67,13 @@ class Reducer:
         self._deferred = False
         self._updated_buckets = 0
         self.packs_current = False     # True after a step whose buckets all re-packed their layers
+        # gradient transport type of the fused reducer: "fp32" (what DDP moves) or "bf16" (cast per bucket,
+        # half the NVLink bytes, fp32 accumulation and update)
+        if grad_dtype not in ("fp32", "bf16"):
+            raise ValueError("grad_dtype must be 'fp32' or 'bf16'")
+        self.grad_bf16 = grad_dtype == "bf16" and self.peer is not None and self.world > 1
+        if self.grad_bf16:
+            self.arena.enable_bf16_grads()
         self.optimizer = None
         self.state_sharded = False
         self.require_sync = True
@@ -233,9 +241,18 @@ class Reducer:
                 opt = self.optimizer
                 m = opt._state_flat[opt.state_names[0]]
                 v = opt._state_flat[opt.state_names[1]] if len(opt.state_names) > 1 else None
-                self.state_sharded = self.state_sharded or bool(two)
-                self.peer.reduce_update(a.grad_buf, a.param_buf, m, v, opt._hyper_dev, off_b, n,
-                                        opt.opt_code, two_shot=two, stream=self.comm_stream)
+                if self.grad_bf16:
+                    from .. import _native as nv
+                    two = two or 1       # the bf16 reducers shard like two-shot / multicast
+                    nv.call("cast_f32_bf16", a.grad_flat[bucket.offset:].data_ptr(),
+                            a.grad16_flat[bucket.offset:].data_ptr(), n, self.comm_stream.cuda_stream)
+                    self.state_sharded = True
+                    self.peer.reduce_update16(a.grad16_buf, a.param_buf, m, v, opt._hyper_dev, off_b, n,
+                                              opt.opt_code, stream=self.comm_stream)
+                else:
+                    self.state_sharded = self.state_sharded or bool(two)
+                    self.peer.reduce_update(a.grad_buf, a.param_buf, m, v, opt._hyper_dev, off_b, n,
+                                            opt.opt_code, two_shot=two, stream=self.comm_stream)
                 self._repack_bucket(bucket)
             else:
                 self.peer.allreduce(a.grad_buf, off_b, n, scale=1.0 / self.world, stream=self.comm_stream)
@@ -342,7 +359,7 @@ class Reducer:
 
 class DistributedModel(nn.Module):
     def __init__(self, module, comm=None, optimizer=None, bucket_cap_mb=25.0, first_bucket_mb=1.0,
-                 broadcast_buffers=True, device_ids=None, output_device=None, dtype=None):
+                 broadcast_buffers=True, device_ids=None, output_device=None, dtype=None, grad_dtype="fp32"):
         super().__init__()
         if dtype is not None:
             from ..ops.modules import set_precision
@@ -350,7 +367,7 @@ class DistributedModel(nn.Module):
         comm = comm or rendezvous.current() or rendezvous.init()
         self.module = module
         self.comm = comm
-        self.reducer = Reducer(module, comm, bucket_cap_mb, first_bucket_mb, broadcast_buffers)
+        self.reducer = Reducer(module, comm, bucket_cap_mb, first_bucket_mb, broadcast_buffers, grad_dtype)
         if optimizer is not None:
             optimizer.attach(self.reducer)
 
@@ -383,7 +400,8 @@ def wrap(model, optimizer=None, comm=None, **kw) -> DistributedModel:
     """``net = wrap(net)`` replaces ``DistributedDataParallel(net, device_ids=[gpu])``.
 
     ``dtype="bf16"`` (default of the layers) or ``dtype="tf32"``: the activation / operand precision
-    of the wrapped model's layers, see ``ops.set_precision``."""
+    of the wrapped model's layers, see ``ops.set_precision``.  ``grad_dtype="bf16"``: gradients cross
+    NVLink as bf16 (cast per bucket, fp32 accumulation and update); default ``"fp32"`` as in DDP."""
     return DistributedModel(model, comm=comm, optimizer=optimizer, **kw)
 
 

@@ -203,6 +203,19 @@ int dtdl_comm_allreduce(void* handle, void* const* grads, void* const* dst, long
 int dtdl_comm_reduce_update(void* handle, void* const* grads, void* const* params, float* mom,
                             float* var, const float* hyper, long long offset_bytes, long long n,
                             int opt, int two_shot, int max_blocks, void* stream);
+/* bf16 gradient transport (option; the north star's "cast fused with the collective and the update"):
+ * dtdl_cast_f32_bf16 fills the bf16 gradient arena, the *16 variants reduce it over NVLink in half the
+ * bytes (fp32 accumulation), apply 1/W + weight decay + SGD/Adam in fp32 and store fp32 parameters to
+ * every rank.  offset_bytes / n address the fp32 arenas (n multiple of 8); the bf16 arena is addressed
+ * at offset_bytes / 2.  The reference's DDP moves fp32 gradients
+ * (pytorch/distributed_data_parallel.py:132), so this is off by default. */
+int dtdl_cast_f32_bf16(const float* src, void* dst, long long n, void* stream);
+int dtdl_comm_reduce_update16(void* handle, void* const* grads16, void* const* params, float* mom,
+                              float* var, const float* hyper, long long offset_bytes, long long n,
+                              int opt, int max_blocks, void* stream);
+int dtdl_comm_nvls_reduce_update16(void* handle, void* mc_grads16, void* mc_params, float* param, float* mom,
+                                   float* var, const float* hyper, long long offset_bytes, long long n,
+                                   int opt, int max_blocks, void* stream);
 int dtdl_comm_broadcast(void* handle, void* const* bufs, long long offset_bytes, long long bytes,
                         int root, int max_blocks, void* stream);
 int dtdl_comm_allgather(void* handle, void* const* bufs, long long offset_bytes, long long bytes,

@@ -183,6 +183,75 @@ def collectives_sweep(i, world, outdir, nvls=False):
     dtdl.shutdown()
 
 
+def bf16_gradient_transport(i, world, outdir, nvls=False):
+    """wrap(..., grad_dtype="bf16"): the kernel-level arithmetic (cast, half-width reduce with fp32
+    accumulation, fused SGD, fp32 parameters stored to every rank) and a short training run."""
+    import distributed_training_dl_b200 as dtdl
+    from distributed_training_dl_b200 import _native as nv
+    from distributed_training_dl_b200.models import MLP
+    comm = _init_nvls(dtdl, outdir, i) if nvls else dtdl.init(backend="b200")
+    if comm is None:
+        return
+    peer, dev = comm.peer, comm.device
+    for numel in (1 << 10, (1 << 20) + 8):
+        g = torch.Generator().manual_seed(17)
+        grads = torch.randn(world, numel, generator=g)
+        p0 = torch.randn(numel, generator=g)
+        gf, g16, params, ms = (peer.alloc(numel * 4), peer.alloc(numel * 2), peer.alloc(numel * 4),
+                               peer.alloc(numel * 4))
+        gf.view(torch.float32, 0, numel).copy_(grads[i])
+        p, m = params.view(torch.float32, 0, numel), ms.view(torch.float32, 0, numel)
+        p.copy_(p0)
+        lr, mu, wd = 0.1, 0.9, 1e-2
+        hyper = torch.tensor([lr, mu, wd, 1.0 / world, 0, 0, 0, 1, 1, 0.0] + [0.0] * 6, device=dev)
+        nv.call("cast_f32_bf16", gf.local_ptr, g16.local_ptr, numel, nv.stream_ptr())
+        assert torch.equal(g16.view(torch.bfloat16, 0, numel).cpu(), grads[i].to(torch.bfloat16))
+        peer.reduce_update16(g16, params, m, None, hyper, 0, numel, 1)
+        torch.cuda.synchronize()
+        gavg = grads.to(torch.bfloat16).float().mean(0)
+        want = p0 - lr * (gavg + wd * p0)
+        # peer pointers: fp32 sum of the bf16 values, exact up to summation order.  Multicast: the switch
+        # returns the fp32-accumulated sum rounded to bf16 (8 mantissa bits) before the 1/W scale.
+        bound = 1e-5 + (lr * 2.0 ** -8 * grads.abs().sum(0).max().item() / world if nvls else 0.0)
+        err = (p.cpu() - want).abs().max().item()
+        assert err < bound, (numel, err, bound)
+        allp = comm.allgather_object(p[:4096].cpu())
+        assert all(torch.equal(allp[0], q) for q in allp), "ranks hold different parameters"
+        comm.barrier()
+    # training through wrap(): tracks single-process fp32 SGD (bf16 rounding of the gradients only)
+    torch.manual_seed(3)
+    mlp = MLP(n_units=64)
+    ref = copy.deepcopy(mlp)
+    net = dtdl.wrap(mlp.to(dev), grad_dtype="bf16")
+    assert net.reducer.grad_bf16
+    opt = dtdl.FusedSGD(net.parameters(), lr=0.05, momentum=0.9)
+    ropt = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9)
+    g = torch.Generator().manual_seed(11)
+    for it in range(3):
+        xs = torch.randn(world, 32, 784, generator=g)
+        ts = torch.randint(0, 10, (world, 32), generator=g)
+        loss = F.cross_entropy(net(xs[i].to(dev)), ts[i].to(dev))
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        rl = F.cross_entropy(ref(xs.reshape(-1, 784)), ts.reshape(-1))
+        ropt.zero_grad()
+        rl.backward()
+        ropt.step()
+    torch.cuda.synchronize()
+    for (n_, q), r in zip(net.module.named_parameters(), ref.parameters()):
+        err = (q.detach().cpu() - r).abs().max().item()
+        assert err < 1e-2, (n_, err)
+    chk = torch.cat([q.detach().flatten()[:64] for q in net.parameters()]).cpu()
+    alls = comm.allgather_object(chk)
+    assert all(torch.equal(alls[0], a) for a in alls), "replicas diverged"
+    sd = opt.state_dict()
+    mb = comm.allgather_object(sd["state"][0]["momentum_buffer"].flatten()[:16].cpu())
+    assert all(torch.equal(mb[0], q) for q in mb)
+    _ok(outdir, i)
+    dtdl.shutdown()
+
+
 def ddp_training(i, world, outdir, use_graph, nvls=False):
     import distributed_training_dl_b200 as dtdl
     from distributed_training_dl_b200.engine import CrossEntropyLoss, TrainStep

@@ -6,7 +6,7 @@ import torch
 
 import distributed_training_dl_b200 as dtdl
 
-from _gpu_workers import collectives, collectives_sweep, ddp_training, ddp_variants
+from _gpu_workers import bf16_gradient_transport, collectives, collectives_sweep, ddp_training, ddp_variants
 
 pytestmark = pytest.mark.gpu
 
@@ -43,6 +43,16 @@ def test_collectives_sweep(tmp_path, nvls):
     """Every variant x 1 KiB .. 64 MiB (1 GiB with DTDL_TEST_MAX_BYTES) x 10 repetitions, bitwise exact."""
     world = _world()
     dtdl.spawn(collectives_sweep, nprocs=world, args=(world, str(tmp_path), nvls))
+    if nvls:
+        _done_or_skipped(tmp_path, world)
+    else:
+        assert all(os.path.exists(tmp_path / f"ok_{i}") for i in range(world))
+
+
+@pytest.mark.parametrize("nvls", [False, True])
+def test_bf16_gradient_transport(tmp_path, nvls):
+    world = _world()
+    dtdl.spawn(bf16_gradient_transport, nprocs=world, args=(world, str(tmp_path), nvls))
     if nvls:
         _done_or_skipped(tmp_path, world)
     else:
