@@ -75,6 +75,10 @@ struct ConvGemmArgs {
   void* y;
   const float* bias;
   float* stats;  // optional [2*Cout_p]: per-channel sum / sum of squares of y (pre-zeroed)
+  // optional second, fp32 copy of the first y2_cols channels, row stride y2_ld floats: the single-process
+  // engine points it at GPU 0's logits buffer, so "gather" is a store of the last layer's epilogue (K-C6)
+  float* y2;
+  int y2_ld, y2_cols;
   ConvTap tap[kMaxTaps];
 };
 
@@ -213,6 +217,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       } else {
         epilogue_store_bf16(reinterpret_cast<__nv_bfloat16*>(a.y) + pix * a.Cout_p + col0, f, a.Cout_p - col0);
       }
+      if (a.y2 != nullptr) {
+        float* o2 = a.y2 + pix * a.y2_ld + col0;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          if (col0 + i < a.y2_cols) o2[i] = f[i];
+      }
     }
     if (a.stats != nullptr) epilogue_stats_flush_parts(s_parts, a.stats, a.n_tile, nt * a.n_tile, a.Cout_p, etid);
   }
@@ -250,7 +260,7 @@ static int launch_conv_taps(const void* x, const void* wpack, void* y, const flo
                             int N, int H, int W, int Cin_p, int gH, int gW, int Cout_p,
                             const ConvTap* taps, int ntaps, int pack_taps, int stride, int oH, int oW,
                             int osh, int osw, int oh0, int ow0, int flags, int act,
-                            cudaStream_t stream) {
+                            cudaStream_t stream, float* y2 = nullptr, int y2_ld = 0, int y2_cols = 0) {
   DTDL_REQUIRE(ntaps >= 1 && ntaps <= kMaxTaps, "between 1 and 64 filter taps per launch");
   const int esz = act_esize(act);
   ConvGemmArgs a;
@@ -304,6 +314,9 @@ static int launch_conv_taps(const void* x, const void* wpack, void* y, const flo
   a.y = y;
   a.bias = bias;
   a.stats = stats;
+  a.y2 = y2;
+  a.y2_ld = y2_ld;
+  a.y2_cols = y2_cols;
 
   CUtensorMap tmA, tmB;
   {
@@ -381,6 +394,34 @@ extern "C" int dtdl_conv_fprop_stats(const void* x, const void* wpack, void* y, 
     }
   return launch_conv_taps(x, wpack, y, bias, stats, N, H, W, Cin_p, Ho, Wo, Cout_p, taps, KH * KW, KH * KW,
                           stride, Ho, Wo, 1, 1, 0, 0, flags, act, stream);
+}
+
+// dtdl_conv_fprop for the LAST layer of a replica in the single-process engine: besides y, the first
+// y2_cols channels are stored as fp32 rows of stride y2_ld floats at y2, which may be (peer-mapped)
+// memory of another GPU -- the logits land in GPU 0's output buffer from the GEMM epilogue, there is
+// no gather pass (nn.DataParallel's gather: pytorch/data_parallel.py:104).  Stride 1.
+extern "C" int dtdl_conv_fprop_gather(const void* x, const void* wpack, void* y, const float* bias,
+                                      float* y2, int y2_ld, int y2_cols, int N, int H, int W, int Cin_p,
+                                      int Ho, int Wo, int Cout_p, int KH, int KW, int pad_h, int pad_w,
+                                      int flags, int act, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  DTDL_REQUIRE(act == kActBf16 || act == kActF32, "act must be 0 (bf16) or 1 (fp32 / TF32)");
+  DTDL_REQUIRE(Cin_p % 8 == 0 && Cout_p % 8 == 0, "channel counts must be padded to 8");
+  DTDL_REQUIRE(KH * KW <= kMaxTaps, "at most 64 filter taps");
+  DTDL_REQUIRE(y2 != nullptr && y2_ld >= y2_cols && y2_cols <= Cout_p, "bad gather destination");
+  DTDL_REQUIRE(Ho >= 1 && Wo >= 1 && Ho <= H + 2 * pad_h - KH + 1 && Wo <= W + 2 * pad_w - KW + 1,
+               "output size does not match the convolution");
+  ConvTap taps[kMaxTaps];
+  for (int r = 0; r < KH; ++r)
+    for (int s = 0; s < KW; ++s) {
+      ConvTap& t = taps[r * KW + s];
+      t.dh = (short)(r - pad_h);
+      t.dw = (short)(s - pad_w);
+      t.k = (short)(r * KW + s);
+      t.pad_ = 0;
+    }
+  return launch_conv_taps(x, wpack, y, bias, nullptr, N, H, W, Cin_p, Ho, Wo, Cout_p, taps, KH * KW, KH * KW, 1,
+                          Ho, Wo, 1, 1, 0, 0, flags, act, stream, y2, y2_ld, y2_cols);
 }
 
 // Data gradient of a stride-2 convolution, gather form.  dx[n,h,w,:] receives, for every filter tap

@@ -1027,7 +1027,8 @@ __global__ void unpad_cast_kernel(const T* __restrict__ x, float* __restrict__ y
 // ---------------------------------------------------------------------------
 __global__ void linear_f32_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                       const float* __restrict__ bias, float* __restrict__ y, int N,
-                                      int K, int Kp, int O, int Op, int relu) {
+                                      int K, int Kp, int O, int Op, int relu, float* __restrict__ y2,
+                                      int y2_ld) {
   const long long total = (long long)N * Op;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -1040,6 +1041,7 @@ __global__ void linear_f32_fwd_kernel(const float* __restrict__ x, const float* 
       for (int k = 0; k < K; ++k) acc = fmaf(xr[k], wr[k], acc);
       if (bias != nullptr) acc += bias[o];
       if (relu) acc = fmaxf(acc, 0.f);
+      if (y2 != nullptr) y2[n * y2_ld + o] = acc;   // second copy, e.g. a row of GPU 0's logits buffer
     }
     y[i] = acc;
   }
@@ -1479,10 +1481,11 @@ extern "C" int dtdl_unpad_cast(const void* x, float* y, long long rows, int cols
   return 0;
 }
 
-extern "C" int dtdl_linear_f32_fwd(const float* x, const float* w, const float* bias, float* y, int N,
-                                   int K, int Kp, int O, int Op, int relu, void* stream) {
+extern "C" int dtdl_linear_f32_fwd(const float* x, const float* w, const float* bias, float* y, float* y2,
+                                   int y2_ld, int N, int K, int Kp, int O, int Op, int relu, void* stream) {
+  DTDL_REQUIRE(y2 == nullptr || y2_ld >= O, "bad gather destination");
   linear_f32_fwd_kernel<<<grid_for((long long)N * Op, 128, kMaxBlocks), 128, 0, STREAM(stream)>>>(
-      x, w, bias, y, N, K, Kp, O, Op, relu);
+      x, w, bias, y, N, K, Kp, O, Op, relu, y2, y2_ld);
   DTDL_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

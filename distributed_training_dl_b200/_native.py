@@ -100,7 +100,7 @@ def check(rc):
 
 
 # kernels launched per native call (everything not listed launches none)
-_LAUNCHES = {"conv_fprop": 1, "conv_fprop_stats": 1, "conv_dgrad_s2": 4, "comm_nvls_allreduce": 1, "comm_reduce_update16": 1, "comm_nvls_reduce_update16": 1, "cast_f32_bf16": 1,
+_LAUNCHES = {"conv_fprop": 1, "conv_fprop_stats": 1, "conv_fprop_gather": 1, "conv_dgrad_s2": 4, "comm_nvls_allreduce": 1, "comm_reduce_update16": 1, "comm_nvls_reduce_update16": 1, "cast_f32_bf16": 1,
              "comm_nvls_reduce_update": 1, "comm_nvls_broadcast": 1, "conv_wgrad": 2, "pack_weights": 1,
              "nchw_to_nhwc": 1, "nchw_to_s2d": 1, "bn_stats": 1, "bn_apply": 1, "bn_apply_stats": 1, "bn_bwd": 2,
              "bn_bwd_add": 2, "bn_bwd_fused": 1, "relu_bwd": 1, "add": 1, "add_prefix": 1, "pool_fwd": 1, "pool_bwd": 1,

@@ -288,7 +288,8 @@ class _LinearF32(torch.autograd.Function):
         x = x.contiguous()
         N, Kp = x.shape[0], x.shape[-1]
         y = torch.empty((N, 1, 1, mod.Cout_p), dtype=torch.float32, device=x.device)
-        nv.call("linear_f32_fwd", nv.ptr(x), nv.ptr(weight), nv.ptr(bias), nv.ptr(y), N, mod.Cin, Kp,
+        y2, y2_ld = getattr(mod, "_gather_dst", None) or (0, 0)
+        nv.call("linear_f32_fwd", nv.ptr(x), nv.ptr(weight), nv.ptr(bias), nv.ptr(y), y2, y2_ld, N, mod.Cin, Kp,
                 mod.Cout, mod.Cout_p, 1 if mod.fuse_relu else 0, nv.stream_ptr())
         ctx.mod = mod
         ctx.has_bias = bias is not None
@@ -335,9 +336,20 @@ class _Conv(torch.autograd.Function):
         if (stats_for is not None and FUSE_BN_STATS
                 and (stats_for.training or stats_for.running_mean is None)):
             stats = _claim_bn_stats(stats_for, x.device, mod.Cout_p)
-        y = conv_fprop_raw(x, mod.wf, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad, bias=bias,
-                           relu=mod.fuse_relu, out_f32=False, out_hw=getattr(mod, "out_hw", None),
-                           stats=stats, stride=mod.conv_stride)
+        gather = getattr(mod, "_gather_dst", None)
+        if gather is not None and mod.conv_stride == 1 and not stats:
+            # last layer of a replica in the single-process engine: the epilogue also stores fp32 logits
+            # into GPU 0's output buffer (no gather pass)
+            N, H, W, Cin_p = x.shape
+            Ho, Wo = _conv_out(H, mod.KH, mod.conv_pad), _conv_out(W, mod.KW, mod.conv_pad)
+            y = torch.empty((N, Ho, Wo, mod.Cout_p), dtype=x.dtype, device=x.device)
+            nv.call("conv_fprop_gather", nv.ptr(x), nv.ptr(mod.wf), nv.ptr(y), nv.ptr(bias), gather[0], gather[1],
+                    mod.Cout, N, H, W, Cin_p, Ho, Wo, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad, mod.conv_pad,
+                    1 if mod.fuse_relu else 0, act_of(x), nv.stream_ptr())
+        else:
+            y = conv_fprop_raw(x, mod.wf, mod.Cout_p, mod.KH, mod.KW, mod.conv_pad, bias=bias,
+                               relu=mod.fuse_relu, out_f32=False, out_hw=getattr(mod, "out_hw", None),
+                               stats=stats, stride=mod.conv_stride)
         ctx.mod = mod
         ctx.has_bias = bias is not None
         ctx.save_for_backward(x, weight, bias, y if mod.fuse_relu else None)

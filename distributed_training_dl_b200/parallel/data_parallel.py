@@ -40,17 +40,20 @@ class _GatherLogits(torch.autograd.Function):
     """
 
     @staticmethod
-    def forward(ctx, C, out_device, world, *xs):
+    def forward(ctx, C, out_device, world, prefilled, *xs):
         ctx.world = world
         N = sum(x.shape[0] for x in xs)
-        out = torch.empty((N, C), dtype=torch.float32, device=out_device)
+        # ``prefilled``: the logits buffer on GPU 0 that every replica's last layer has already stored
+        # its rows into from its GEMM epilogue (K-C6); otherwise a conversion kernel per replica does it
+        out = prefilled if prefilled is not None else torch.empty((N, C), dtype=torch.float32, device=out_device)
         main = torch.cuda.current_stream(out_device)
         row, meta = 0, []
         for x in xs:
             n, Cp = x.shape[0], x.shape[-1]
             with torch.cuda.device(x.device):
                 st = torch.cuda.current_stream(x.device)
-                nv.call("unpad_cast", nv.ptr(x), out[row: row + n].data_ptr(), n, C, Cp, fn.act_of(x), st.cuda_stream)
+                if prefilled is None:
+                    nv.call("unpad_cast", nv.ptr(x), out[row: row + n].data_ptr(), n, C, Cp, fn.act_of(x), st.cuda_stream)
                 ev = torch.cuda.Event()
                 ev.record(st)
             main.wait_event(ev)
@@ -76,7 +79,7 @@ class _GatherLogits(torch.autograd.Function):
                 dx = torch.empty((n, 1, 1, Cp), dtype=dtype, device=dev)
                 nv.call("pad_cast", dy[row: row + n].data_ptr(), nv.ptr(dx), n, ctx.C, Cp, fn.act_of(dtype), st.cuda_stream)
             grads.append(dx)
-        return (None, None, None) + tuple(grads)
+        return (None, None, None, None) + tuple(grads)
 
 
 class _ShardLoss(torch.autograd.Function):
@@ -222,12 +225,38 @@ class DataParallel(nn.Module):
                 if train:
                     self.sync_buffers_on(g)
         outs = []
+        # gather folded into the replicas' last layer: its epilogue stores fp32 logits straight into this
+        # buffer on GPU 0 (peer write over NVLink) when the model ends in Linear -> OutputLayout
+        heads = self._gather_heads()
+        logits = (torch.empty((x.shape[0], self.out_features), dtype=torch.float32, device=d0)
+                  if heads is not None else None)
         for g, (lo, hi) in enumerate(self.shard_bounds(x.shape[0])):
             if lo >= hi:
                 continue
             with torch.cuda.device(self.devices[g]):
-                outs.append(self.run_replica_body(g, x[lo:hi]))
-        return _GatherLogits.apply(self.out_features, d0, self.world, *outs)
+                if heads is not None:
+                    heads[g]._gather_dst = (logits[lo:hi].data_ptr(), self.out_features)
+                try:
+                    outs.append(self.run_replica_body(g, x[lo:hi]))
+                finally:
+                    if heads is not None:
+                        heads[g]._gather_dst = None
+        return _GatherLogits.apply(self.out_features, d0, self.world, logits, *outs)
+
+    def _gather_heads(self):
+        """The replicas' final Linear layers when the model ends in ``Linear -> OutputLayout`` with
+        matching widths and no fused activation (then their epilogue can write GPU 0's logits);
+        None otherwise."""
+        if not hasattr(self, "_heads"):
+            from ..ops.modules import Linear
+            heads = []
+            for rep in self.replicas:
+                mods = [m for m in rep.modules() if len(list(m.children())) == 0]
+                ok = (len(mods) >= 2 and isinstance(mods[-1], OutputLayout) and isinstance(mods[-2], Linear)
+                      and mods[-2].out_features == self.out_features and not mods[-2].fuse_relu)
+                heads.append(mods[-2] if ok else None)
+            self._heads = heads if all(h is not None for h in heads) else None
+        return self._heads
 
     # ------------------------------------------------------------------ reducer interface (FusedSGD)
     def finish_step(self, fused=True):

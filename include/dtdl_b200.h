@@ -45,6 +45,14 @@ int dtdl_conv_fprop_stats(const void* x, const void* wpack, void* y, const float
                           int N, int H, int W, int Cin_p, int Ho, int Wo, int Cout_p, int KH, int KW,
                           int pad_h, int pad_w, int flags, int stride, int act, void* stream);
 
+/* dtdl_conv_fprop for a replica's LAST layer in the single-process engine: the first y2_cols output
+ * channels are also stored as fp32 rows (stride y2_ld floats) at y2, which may be peer-mapped memory of
+ * GPU 0 -- nn.DataParallel's gather (pytorch/data_parallel.py:104) becomes a store of the GEMM epilogue. */
+int dtdl_conv_fprop_gather(const void* x, const void* wpack, void* y, const float* bias, float* y2,
+                           int y2_ld, int y2_cols, int N, int H, int W, int Cin_p, int Ho, int Wo,
+                           int Cout_p, int KH, int KW, int pad_h, int pad_w, int flags, int act,
+                           void* stream);
+
 /* Data gradient of a stride-2 convolution (pytorch/model.py:28-29 with stride=2 from :69,71) in
  * gather form: four launches, one per output phase (h%2, w%2), each a stride-1 convolution over
  * dy [N,Hy,Wy,Cout_p] with the taps that reach that phase, stored to every other pixel of
@@ -156,8 +164,9 @@ int dtdl_unpad_cast(const void* x, float* y, long long rows, int cols, int cols_
 /* Full-fp32 Linear on CUDA cores for the fp32 activation mode: torch keeps TF32 off for matmuls,
  * so the reference's nn.Linear (pytorch/model.py:77,111) is plain fp32.  x [N][Kp], y / dy [N][Op]
  * fp32 padded rows; w [O][K], dw [O][K]; dx may be null (first layer). */
-int dtdl_linear_f32_fwd(const float* x, const float* w, const float* bias, float* y, int N, int K,
-                        int Kp, int O, int Op, int relu, void* stream);
+int dtdl_linear_f32_fwd(const float* x, const float* w, const float* bias, float* y,
+                        float* y2 /* optional second copy, rows of y2_ld floats (may be peer memory) */,
+                        int y2_ld, int N, int K, int Kp, int O, int Op, int relu, void* stream);
 int dtdl_linear_f32_bwd(const float* dy, const float* x, const float* w, float* dx, float* dw, int N,
                         int K, int Kp, int O, int Op, int accumulate, void* stream);
 

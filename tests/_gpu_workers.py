@@ -212,7 +212,8 @@ def bf16_gradient_transport(i, world, outdir, nvls=False):
         want = p0 - lr * (gavg + wd * p0)
         # peer pointers: fp32 sum of the bf16 values, exact up to summation order.  Multicast: the switch
         # returns the fp32-accumulated sum rounded to bf16 (8 mantissa bits) before the 1/W scale.
-        bound = 1e-5 + (lr * 2.0 ** -8 * grads.abs().sum(0).max().item() / world if nvls else 0.0)
+        in_switch = peer.use_nvls and bool(g16.mc_ptr)      # also when NVLS switched itself on (world >= 4)
+        bound = 1e-5 + (lr * 2.0 ** -8 * grads.abs().sum(0).max().item() / world if in_switch else 0.0)
         err = (p.cpu() - want).abs().max().item()
         assert err < bound, (numel, err, bound)
         allp = comm.allgather_object(p[:4096].cpu())

@@ -6,7 +6,7 @@ mkdir -p gpurun_out
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 step() { echo "=== $* ($(date +%T))"; }
 step tests
-DTDL_TEST_WORLD=$N DTDL_TEST_MAX_BYTES=$((1 << 30)) timeout 420 python -m pytest tests/test_comm_gpu.py -x -q -s -m gpu -k "sweep or ddp_training" \
+DTDL_TEST_WORLD=$N DTDL_TEST_MAX_BYTES=$((1 << 30)) timeout 420 python -m pytest tests/test_comm_gpu.py -x -q -s -m gpu -k "sweep or ddp_training or bf16" \
   > gpurun_out/comm_tests_w${N}.log 2>&1
 grep -c "exact on every rank" gpurun_out/comm_tests_w${N}.log; tail -2 gpurun_out/comm_tests_w${N}.log
 step timeline
