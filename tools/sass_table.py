@@ -17,11 +17,17 @@ COLUMNS = [("UTCHMMA", r"\bUTCHMMA"), ("UTMALDG", r"\bUTMALDG"), ("LDTM", r"\bLD
            ("UTC barrier/alloc", r"\bUTCBAR|\bUTCATOMSWS|\bUTCCP"), ("SYNCS", r"\bSYNCS"), ("HMMA", r"\bHMMA"),
            ("LDG", r"\bLDG\b|\bLDG\."), ("LDGMC", r"\bLDGMC"), ("STG", r"\bSTG"), ("RED/ATOM", r"\bREDG?\b|\bREDG?\.|\bATOM"),
            ("SHFL", r"\bSHFL"), ("MEMBAR", r"\bMEMBAR")]
-LISTINGS = {"conv_gemm_kernel": "conv_gemm.sass", "conv_gemm_v2_kernel": "conv_gemm_v2.sass",
-            "conv_wgrad_kernel": "conv_wgrad.sass", "bn_apply_kernel": "bn_apply.sass",
-            "bn_apply_stats_kernel": "bn_apply_stats.sass", "bn_bwd_apply_kernel": "bn_bwd_apply.sass",
-            "softmax_ce_kernel": "softmax_ce.sass", "broadcast_kernel": "broadcast.sass",
-            "reduce_kernelILi8E": "reduce_fused.sass", "nvls_reduce_kernel": "nvls_reduce.sass",
+# mangled-name fragment -> listing file (ILi0E = bf16 instantiation, ILi1E = fp32 / TF32; the bandwidth
+# kernels are templated on channels per 16-byte vector: ILi8E = bf16, ILi4E = fp32)
+LISTINGS = {"conv_gemm_kernelILi0E": "conv_gemm.sass", "conv_gemm_kernelILi1E": "conv_gemm_tf32.sass",
+            "conv_gemm_v2_kernelILi0E": "conv_gemm_v2.sass", "conv_gemm_v2_kernelILi1E": "conv_gemm_v2_tf32.sass",
+            "conv_wgrad_kernelILi0E": "conv_wgrad.sass", "conv_wgrad_kernelILi1E": "conv_wgrad_tf32.sass",
+            "bn_apply_kernelILi8E": "bn_apply.sass", "bn_apply_stats_kernelILi8E": "bn_apply_stats.sass",
+            "bn_bwd_apply_kernelILi8E": "bn_bwd_apply.sass", "bn_bwd_fused_kernelILi8E": "bn_bwd_fused.sass",
+            "bn_bwd_fused_kernelILi4E": "bn_bwd_fused_fp32.sass",
+            "softmax_ce_kernel": "softmax_ce.sass", "18broadcast_kernel": "broadcast.sass",
+            "13reduce_kernelILi8E": "reduce_fused.sass", "nvls_reduce_kernelILi4ELi512E": "nvls_reduce.sass",
+            "nvls_reduce16_kernel": "nvls_reduce_bf16.sass", "11sync_kernel": "sync_flags.sass",
             "pack_weights_kernel": "pack_weights.sass"}
 
 
@@ -47,7 +53,9 @@ def main():
     rows.sort(key=lambda r: (-r[2][0], -r[2][1], r[0]))
     with open(os.path.join(OUT, "README.md"), "w") as f:
         f.write("# SASS evidence (`cuobjdump -sass` of libdtdl_b200.so, sm_100a; regenerate with `python tools/sass_table.py`)\n\n")
-        f.write("Instruction counts per kernel.  `UTCHMMA` = tcgen05.mma, `UTMALDG` = TMA tensor load, `LDTM` = "
+        f.write("Instruction counts per kernel.  `UTCHMMA` = tcgen05.mma (kind::f16 and kind::tf32 both assemble to it; the "
+                "`ILi0E` instantiations of the conv kernels are the bf16 ones, `ILi1E` the fp32 / TF32 ones; for the "
+                "bandwidth kernels `ILi8E` = bf16 vectors of 8 channels, `ILi4E` = fp32 vectors of 4), `UTMALDG` = TMA tensor load, `LDTM` = "
                 "tcgen05.ld, `SYNCS` = mbarrier operations, `LDGMC` = multimem.ld_reduce (in-switch reduction; the "
                 "matching multimem.st is an `STG.E.128.STRONG.SYS` to the multicast address).  No `HMMA` (legacy "
                 "mma.sync) anywhere.  The collective kernels dereference peer pointers with plain `LDG`/`STG` (peer "
