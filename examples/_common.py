@@ -31,6 +31,8 @@ def pytorch_flags(description, distributed=False):
     p.add_argument("--synthetic", type=int, default=0, metavar="N",
                    help="train on N random CIFAR-shaped images instead of CIFAR-10")
     p.add_argument("--no-graph", action="store_true", help="eager launches instead of a CUDA graph")
+    p.add_argument("--precision", default="bf16", choices=["bf16", "tf32"],
+                   help="bf16 (fast) or tf32 = fp32 tensors with TF32 convolutions, the reference's precision")
     if distributed:
         p.add_argument("--init-method", default=None,
                        help="tcp://host:port (with --rank/--world-size), env://, slurm; default: auto")

@@ -20,7 +20,8 @@ def main():
     loader = torch.utils.data.DataLoader(cifar_dataset(args), batch_size=args.batch_size, shuffle=True,
                                          num_workers=args.num_workers, drop_last=True)
     print("==> Making model..")
-    model = dtdl.DataParallel(dtdl.models.pyramidnet(), device_ids=list(range(args.gpu_nums)))
+    model = dtdl.DataParallel(dtdl.set_precision(dtdl.models.pyramidnet(), args.precision),
+                              device_ids=list(range(args.gpu_nums)))
     print("The number of parameters of model is", sum(p.numel() for p in model.parameters() if p.requires_grad))
     optimizer = dtdl.FusedSGD(model.parameters(), lr=args.learning_rate, momentum=args.momentum,
                               weight_decay=args.weight_decay)

@@ -67,8 +67,6 @@ def main_worker(local_rank, args):
 def main():
     parser = pytorch_flags("B200-native CIFAR-10 training, one process per GPU", distributed=True)
     parser.add_argument("--spawn", type=int, default=0, help="start N local worker processes")
-    parser.add_argument("--precision", default="bf16", choices=["bf16", "tf32"],
-                        help="bf16 (fast) or tf32 = fp32 tensors with TF32 convolutions, the reference's precision")
     parser.add_argument("--bucket-timing", action="store_true",
                         help="report per-bucket all-reduce time and bus bandwidth after each epoch")
     args = parser.parse_args()

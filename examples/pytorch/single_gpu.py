@@ -21,7 +21,7 @@ def main():
     loader = torch.utils.data.DataLoader(cifar_dataset(args), batch_size=args.batch_size, shuffle=True,
                                          num_workers=args.num_workers, drop_last=True)
     print("==> Making model..")
-    net = dtdl.wrap(dtdl.models.pyramidnet().to(device), comm=comm)
+    net = dtdl.wrap(dtdl.models.pyramidnet().to(device), comm=comm, dtype=args.precision if device.type == "cuda" else None)
     print("The number of parameters of model is", sum(p.numel() for p in net.parameters() if p.requires_grad))
     optimizer = dtdl.FusedSGD(net.parameters(), lr=args.learning_rate, momentum=args.momentum,
                               weight_decay=args.weight_decay)

@@ -354,3 +354,48 @@ def test_train_meter_log_line_and_rank_prefix(capsys):
     assert line.startswith("Epoch:[3][20/782]| loss: 1.000 | acc: 87.500 | batch time: 0.012s")
     RankLogger().info("hello")
     assert "hello" in capsys.readouterr().out
+
+
+def test_bucket_plan_keeps_the_last_bucket_small():
+    """The final bucket (earliest layers, ready only when backward ends) is capped at 4 MiB; buckets
+    tile the arena without gaps and every offset is 32-byte aligned."""
+    from distributed_training_dl_b200.models import pyramidnet
+    from distributed_training_dl_b200.parallel.arena import ParamArena
+    arena = ParamArena(pyramidnet().parameters(), "cpu")
+    sizes = [b.numel * 4 for b in arena.buckets]
+    assert sizes[-1] <= 4 << 20 and len(sizes) >= 4
+    off = 0
+    for b in arena.buckets:
+        assert b.offset == off and b.offset % 8 == 0 and b.numel % 8 == 0
+        off += b.numel
+    assert off == arena.numel
+    assert sorted(id(p) for b in arena.buckets for p in b.params) == sorted(id(p) for p in arena.params)
+
+
+def test_set_precision_marks_every_layer():
+    import torch
+    from distributed_training_dl_b200.models import pyramidnet, resnet50
+    from distributed_training_dl_b200.ops import InputLayout, set_precision
+    from distributed_training_dl_b200.ops.modules import _PackedWeightMixin
+    for make in (pyramidnet, resnet50):
+        m = set_precision(make(), "tf32")
+        layers = [x for x in m.modules() if isinstance(x, (_PackedWeightMixin, InputLayout))]
+        assert layers and all(x.act_dtype == torch.float32 for x in layers)
+        ops = [x._op for x in m.modules() if isinstance(getattr(x, "_op", None), _PackedWeightMixin)]
+        assert all(o.act_dtype == torch.float32 for o in ops)
+        set_precision(m, "bf16")
+        assert all(x.act_dtype == torch.bfloat16 for x in layers)
+    import pytest
+    with pytest.raises(ValueError):
+        set_precision(pyramidnet(), "fp8")
+
+
+def test_data_parallel_shards_are_balanced():
+    from distributed_training_dl_b200.parallel.data_parallel import DataParallel
+    dp = DataParallel.__new__(DataParallel)       # only the arithmetic: no GPUs needed
+    dp.world = 8
+    assert dp.shard_bounds(41) == [(0, 6), (6, 11), (11, 16), (16, 21), (21, 26), (26, 31), (31, 36), (36, 41)]
+    assert dp.shard_bounds(64)[-1] == (56, 64)
+    import pytest
+    with pytest.raises(ValueError):
+        dp.shard_bounds(7)
