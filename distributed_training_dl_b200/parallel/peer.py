@@ -399,12 +399,44 @@ class PeerComm:
     def _stream(self, stream):
         return (stream or torch.cuda.current_stream(self.device)).cuda_stream
 
+    # Variant per message size, per world size, from the measured sweeps (profiles/round2/w{4,8}/
+    # allreduce_sweep_*.md, profiles/allreduce_sweep_2gpu.md): rows of (largest message in bytes, variant),
+    # first match wins; 0 = one-shot, 1 = two-shot, 2 = NVSwitch multicast (falls back to two-shot where
+    # the buffers have no multicast mapping).  World sizes not listed use the next smaller entry.
+    # DTDL_VARIANT_TABLE=/path/table.json ({"8": [[65536, 0], [null, 2]], ...}) replaces it.
+    VARIANT_TABLE = {
+        2: [(256 << 10, 0), (None, 1)],       # one-shot 20-23 us up to 256 KiB; two-shot wins above
+        4: [(None, 2)],                        # multicast <= the others at every size measured
+        8: [(None, 2)],
+    }
+    _variant_table = None
+
+    @classmethod
+    def variant_table(cls):
+        if cls._variant_table is None:
+            table = {w: list(rows) for w, rows in cls.VARIANT_TABLE.items()}
+            path = os.environ.get("DTDL_VARIANT_TABLE")
+            if path:
+                import json
+                with open(path) as f:
+                    table = {int(w): [(None if lim is None else int(lim), int(v)) for lim, v in rows]
+                             for w, rows in json.load(f).items()}
+            cls._variant_table = table
+        return cls._variant_table
+
     def choose_two_shot(self, nbytes: int) -> int:
-        """One-shot (0) below the measured crossover, two-shot (1) above (see
-        profiles/allreduce_sweep.md); 2 = the multicast variant, which shards work like two-shot."""
-        if self.use_nvls and self.world > 1 and nbytes >= self.nvls_min_bytes:
-            return 2
-        return 1 if (self.world > 1 and nbytes >= self.two_shot_min_bytes) else 0
+        """The all-reduce variant for a message of ``nbytes``: 0 = one-shot, 1 = two-shot, 2 = multicast
+        (looked up in ``VARIANT_TABLE``; multicast rows apply only when this communicator runs NVLS)."""
+        if self.world <= 1:
+            return 0
+        table = self.variant_table()
+        key = max((w for w in table if w <= self.world), default=min(table))
+        for limit, variant in table[key]:
+            if limit is None or nbytes <= limit:
+                if variant == 2 and not (self.use_nvls and nbytes >= self.nvls_min_bytes):
+                    variant = 1 if nbytes >= self.two_shot_min_bytes else 0
+                return variant
+        return 1
 
     def _nvls_ok(self, a: SymmBuffer, b: SymmBuffer, nbytes: int) -> bool:
         """Multicast path possible: both buffers are bound to a multicast object and the message

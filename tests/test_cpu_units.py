@@ -399,3 +399,27 @@ def test_data_parallel_shards_are_balanced():
     import pytest
     with pytest.raises(ValueError):
         dp.shard_bounds(7)
+
+
+def test_collective_variant_table(tmp_path, monkeypatch):
+    """Variant choice per message size comes from a table (measured sweeps), overridable from a file."""
+    import json
+    from distributed_training_dl_b200.parallel.peer import PeerComm
+    pc = PeerComm.__new__(PeerComm)
+    pc.two_shot_min_bytes, pc.nvls_min_bytes = 256 * 1024, 0
+    PeerComm._variant_table = None
+    pc.world, pc.use_nvls = 2, False
+    assert [pc.choose_two_shot(n) for n in (1024, 256 << 10, (256 << 10) + 16, 64 << 20)] == [0, 0, 1, 1]
+    pc.world, pc.use_nvls = 8, True
+    assert pc.choose_two_shot(1024) == 2 and pc.choose_two_shot(1 << 30) == 2
+    pc.use_nvls = False                      # multicast rows fall back to the peer-pointer variants
+    assert pc.choose_two_shot(1024) == 0 and pc.choose_two_shot(1 << 24) == 1
+    pc.world = 1
+    assert pc.choose_two_shot(1 << 24) == 0
+    path = tmp_path / "table.json"
+    path.write_text(json.dumps({"8": [[65536, 0], [None, 2]]}))
+    monkeypatch.setenv("DTDL_VARIANT_TABLE", str(path))
+    PeerComm._variant_table = None
+    pc.world, pc.use_nvls = 8, True
+    assert pc.choose_two_shot(4096) == 0 and pc.choose_two_shot(1 << 20) == 2
+    PeerComm._variant_table = None
