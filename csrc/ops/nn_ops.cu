@@ -1029,21 +1029,28 @@ __global__ void linear_f32_fwd_kernel(const float* __restrict__ x, const float* 
                                       const float* __restrict__ bias, float* __restrict__ y, int N,
                                       int K, int Kp, int O, int Op, int relu, float* __restrict__ y2,
                                       int y2_ld) {
+  // one warp per output element: the lanes stride over K (coalesced reads of the x row and the w row)
+  // and combine with shuffles -- a thread per output would walk K serially, one dependent load at a time
+  const int lane = threadIdx.x & 31;
   const long long total = (long long)N * Op;
-  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
+  const long long warps = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < total; i += warps) {
     const int o = (int)(i % Op);
     const long long n = i / Op;
     float acc = 0.f;
     if (o < O) {
       const float* xr = x + n * Kp;
       const float* wr = w + (long long)o * K;
-      for (int k = 0; k < K; ++k) acc = fmaf(xr[k], wr[k], acc);
+      for (int k = lane; k < K; k += 32) acc = fmaf(xr[k], wr[k], acc);
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
       if (bias != nullptr) acc += bias[o];
       if (relu) acc = fmaxf(acc, 0.f);
-      if (y2 != nullptr) y2[n * y2_ld + o] = acc;   // second copy, e.g. a row of GPU 0's logits buffer
     }
-    y[i] = acc;
+    if (lane == 0) {
+      if (o < O && y2 != nullptr) y2[n * y2_ld + o] = acc;   // second copy, e.g. a row of GPU 0's logits buffer
+      y[i] = acc;
+    }
   }
 }
 __global__ void linear_f32_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w,
@@ -1484,8 +1491,8 @@ extern "C" int dtdl_unpad_cast(const void* x, float* y, long long rows, int cols
 extern "C" int dtdl_linear_f32_fwd(const float* x, const float* w, const float* bias, float* y, float* y2,
                                    int y2_ld, int N, int K, int Kp, int O, int Op, int relu, void* stream) {
   DTDL_REQUIRE(y2 == nullptr || y2_ld >= O, "bad gather destination");
-  linear_f32_fwd_kernel<<<grid_for((long long)N * Op, 128, kMaxBlocks), 128, 0, STREAM(stream)>>>(
-      x, w, bias, y, N, K, Kp, O, Op, relu, y2, y2_ld);
+  linear_f32_fwd_kernel<<<grid_for((long long)N * Op, 8, kMaxBlocks), 256, 0, STREAM(stream)>>>(
+      x, w, bias, y, N, K, Kp, O, Op, relu, y2, y2_ld);   // 8 warps = 8 outputs per block
   DTDL_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
