@@ -68,29 +68,39 @@ class _PackedWeightMixin:
 
 
 def pack_weights(modules, table_cache=None):
-    """Packs the weights of ``modules`` (conv / linear layers on one device) in one launch."""
+    """Packs the weights of ``modules`` (conv / linear layers on one device) in one launch.
+
+    ``table_cache``: a dict that keeps the device-side layer table between calls.  It is keyed by the
+    addresses it describes, so re-allocated packs (a precision switch, a move to another device) or
+    re-pointed weights rebuild it instead of sending the kernel to freed memory."""
     modules = [m for m in modules if isinstance(m, _PackedWeightMixin)]
     if not modules:
         return None
-    if table_cache is not None and table_cache.get("table") is not None:
+    for m in modules:
+        if m._packs_stale():
+            m._alloc_packs(m.weight.device)
+
+    def src_of(m):
+        src = getattr(m, "pack_src", None)
+        return src if src is not None else m.weight
+
+    key = tuple((src_of(m).data_ptr(), m.wf.data_ptr(), m.wd.data_ptr() if m.wd is not None else 0) for m in modules)
+    if table_cache is not None and table_cache.get("table") is not None and table_cache.get("key") == key:
         table, n, blocks = table_cache["table"], table_cache["n"], table_cache["blocks"]
     else:
         esz = nv.lib().dtdl_pack_entry_size()
         host = (ctypes.c_char * (esz * len(modules)))()
         blocks = 0
         for i, m in enumerate(modules):
-            if m._packs_stale():
-                m._alloc_packs(m.weight.device)
             entry = ctypes.addressof(host) + i * esz
-            src = getattr(m, "pack_src", None)
             blocks += nv.lib().dtdl_pack_entry_fill(
-                entry, nv.ptr(src if src is not None else m.weight), nv.ptr(m.wf), nv.ptr(m.wd), m.Cout, m.Cin, m.KH * m.KW,
+                entry, nv.ptr(src_of(m)), nv.ptr(m.wf), nv.ptr(m.wd), m.Cout, m.Cin, m.KH * m.KW,
                 m.Cin_p, m.Cout_p, blocks, fn.act_of(m.wf))
         dev = modules[0].weight.device
         table = torch.frombuffer(bytearray(bytes(host)), dtype=torch.uint8).to(dev)
         n = len(modules)
         if table_cache is not None:
-            table_cache.update(table=table, n=n, blocks=blocks)
+            table_cache.update(table=table, n=n, blocks=blocks, key=key)
     nv.call("pack_weights", nv.ptr(table), n, blocks, nv.stream_ptr())
     for m in modules:
         m._packed_version = m.weight._version

@@ -254,3 +254,30 @@ def test_train_step_tf32_graph_matches_eager():
         assert losses[True][-1] == losses[True][-1]
     finally:
         dtdl.shutdown()
+
+
+def test_precision_switch_between_steps_rebuilds_packs():
+    """set_precision on a live, wrapped model: the operand packs are re-allocated in the new type and the
+    cached pack tables (keyed by the addresses they describe) are rebuilt, so eager training goes on."""
+    import distributed_training_dl_b200 as dtdl
+    from distributed_training_dl_b200.models import PyramidNet
+    torch.manual_seed(0)
+    dtdl.init(backend="b200")
+    try:
+        net = dtdl.wrap(PyramidNet(num_layers=3, alpha=45.0).cuda())
+        opt = dtdl.FusedSGD(net.parameters(), lr=0.05, momentum=0.9)
+        x = torch.randn(16, 3, 32, 32, device="cuda")
+        t = torch.randint(0, 10, (16,), device="cuda")
+        losses = []
+        for prec in ("bf16", "bf16", "tf32", "tf32", "bf16", "bf16"):
+            dtdl.set_precision(net, prec)
+            loss = F.cross_entropy(net(x), t)
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            losses.append(loss.item())
+        torch.cuda.synchronize()
+        assert all(l == l for l in losses), losses
+        assert losses[-1] < losses[0], losses          # same batch every step: the loss must fall
+    finally:
+        dtdl.shutdown()
