@@ -194,16 +194,23 @@ class DataParallel(nn.Module):
             if fused:
                 opt._local_update_on(g)
             return
-        for bucket in a.buckets:
-            off_b, n = bucket.offset * 4, bucket.numel
-            two = pc.choose_two_shot(n * 4)
-            self.state_sharded = self.state_sharded or bool(two)
-            if fused:
-                m, v = opt._state_on(g)
-                pc.reduce_update(a.grad_buf, a.param_buf, m, v, opt._hyper_on(g), off_b, n, opt.opt_code,
-                                 two_shot=two, max_blocks=64)
-            else:
-                pc.allreduce(a.grad_buf, off_b, n, scale=1.0 / self.world, max_blocks=64)
+        # the buckets touch disjoint memory: one closing "done" exchange for all of them (see
+        # csrc/comm/collectives.cu), not one per bucket
+        pc.defer_done(True)
+        try:
+            for bucket in a.buckets:
+                off_b, n = bucket.offset * 4, bucket.numel
+                two = pc.choose_two_shot(n * 4)
+                self.state_sharded = self.state_sharded or bool(two)
+                if fused:
+                    m, v = opt._state_on(g)
+                    pc.reduce_update(a.grad_buf, a.param_buf, m, v, opt._hyper_on(g), off_b, n, opt.opt_code,
+                                     two_shot=two, max_blocks=64)
+                else:
+                    pc.allreduce(a.grad_buf, off_b, n, scale=1.0 / self.world, max_blocks=64)
+            pc.barrier()
+        finally:
+            pc.defer_done(False)
 
     # ------------------------------------------------------------------ nn.DataParallel contract
     def forward(self, x):

@@ -142,6 +142,12 @@ class Reducer:
         self._launched_any = False
         self._updated_buckets = 0
         self.packs_current = False
+        if self._deferred and self.peer is not None:
+            # a previous iteration was abandoned between its first bucket and finish_step (an exception,
+            # a backward without a step): close its sequence so that later collectives are self-contained
+            self.peer.barrier(stream=self.comm_stream)
+            self.peer.defer_done(False)
+            self._deferred = False
         if self.optimizer is not None:
             self.optimizer.refresh_hyper()
 
