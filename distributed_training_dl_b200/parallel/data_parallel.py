@@ -20,6 +20,8 @@ GPU 0, ``.module`` is the original model, ``state_dict()`` keys carry ``module.`
 from __future__ import annotations
 
 import copy
+import gc
+import weakref
 
 import torch
 import torch.nn as nn
@@ -248,7 +250,19 @@ class DataParallel(nn.Module):
                 finally:
                     if heads is not None:
                         heads[g]._gather_dst = None
-        return _GatherLogits.apply(self.out_features, d0, self.world, logits, *outs)
+        out = _GatherLogits.apply(self.out_features, d0, self.world, logits, *outs)
+        # DataParallelStep refuses to capture while this call's autograd graph is still alive
+        self._eager_graph = weakref.ref(out.grad_fn) if out.grad_fn is not None else None
+        return out
+
+    def eager_graph_alive(self):
+        """True while the autograd graph of the last eager ``forward`` call is still referenced (by a
+        loss, an output, a saved list ...), after a garbage collection has had its chance."""
+        ref = getattr(self, "_eager_graph", None)
+        if ref is None or ref() is None:
+            return False
+        gc.collect()
+        return ref() is not None
 
     def _gather_heads(self):
         """The replicas' final Linear layers when the model ends in ``Linear -> OutputLayout`` with
@@ -301,9 +315,10 @@ class DataParallelStep:
     backward, fused bucket all-reduce + optimizer update, weight re-pack -- is captured into one
     CUDA graph per GPU and replayed.  Returns a device tensor ``[mean loss, #correct]`` on GPU 0.
 
-    Known limitation: an autograd graph built through ``DataParallel.forward`` (the eager call
-    contract) must not be alive when the capture happens -- drop such a ``loss`` first; CUDA
-    otherwise reports a dependency of the captured stream on uncaptured work.
+    An autograd graph built through ``DataParallel.forward`` (the eager call contract) must not be
+    alive when the capture happens: CUDA would report a dependency of the captured stream on
+    uncaptured work.  The step checks for it and raises a RuntimeError that says so -- drop the
+    eager call's ``loss`` / output first.
     """
 
     def __init__(self, model: DataParallel, optimizer, graph=True, warmup=2):
@@ -389,6 +404,11 @@ class DataParallelStep:
             self._st.copy_(t, non_blocking=True)
             self._stats.zero_()
         if self.use_graph and self._graphs is None and self._calls >= self.warmup:
+            if m.eager_graph_alive():
+                raise RuntimeError(
+                    "DataParallelStep: the autograd graph of an earlier eager model(x) call is still alive "
+                    "(a loss or output tensor of it is referenced); delete it before the step captures its "
+                    "CUDA graphs, or construct the step with graph=False")
             for d in m.devices:
                 torch.cuda.synchronize(d)
             nv.reset_launch_count()

@@ -389,6 +389,17 @@ def data_parallel_engine(outdir):
             raise AssertionError("a batch smaller than the GPU count must be rejected")
         except ValueError:
             pass
+    # an eager call's autograd graph that is still alive when the step wants to capture is reported by
+    # the step itself instead of surfacing as a CUDA capture error
+    held = F.cross_entropy(dp(x), t)
+    refused = dtdl.DataParallelStep(dp, opt, graph=True, warmup=0)
+    try:
+        refused(x.cpu().pin_memory(), t.cpu().pin_memory())
+        raise AssertionError("capture with a live eager autograd graph must be refused")
+    except RuntimeError as e:
+        assert "still alive" in str(e), e
+    del held, refused
+    assert not dp.eager_graph_alive()
     # graph fast path
     step = dtdl.DataParallelStep(dp, opt, graph=True, warmup=2)
     xs, ts = x.cpu().pin_memory(), t.cpu().pin_memory()

@@ -88,6 +88,21 @@ def test_data_parallel_engine(tmp_path, nvls):
     assert res.returncode == 0 and os.path.exists(tmp_path / "ok_dp"), res.stdout[-2000:] + res.stderr[-4000:]
 
 
+def test_data_parallel_engine_one_gpu(tmp_path):
+    """The same engine checks with ONE visible GPU (a single replica): runs on a 1-GPU box, where the
+    multi-GPU variants above are skipped -- eager call contract, live-graph refusal, graph fast path,
+    equivalence with torch SGD, optimizer state format."""
+    if torch.cuda.device_count() < 1:
+        pytest.skip("needs a GPU")
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    code = f"import sys; sys.path.insert(0, {here!r}); import _gpu_workers as w; w.data_parallel_engine({str(tmp_path)!r})"
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
+                         env=dict(os.environ, CUDA_VISIBLE_DEVICES="0", DTDL_NVLS="0"))
+    assert res.returncode == 0 and os.path.exists(tmp_path / "ok_dp"), res.stdout[-2000:] + res.stderr[-4000:]
+
+
 @pytest.mark.parametrize("backend", ["b200", "nccl"])
 def test_ddp_backends_optimizers_no_sync(tmp_path, backend):
     world = _world()
