@@ -66,7 +66,10 @@ class TrainStep:
         self.optimizer.zero_grad()
         loss.backward()
         self.optimizer.step()
-        return loss, getattr(self.criterion, "last_stats", None)
+        # detached: a caller that keeps the returned loss must not keep this step's autograd graph alive
+        # (its gradient-accumulation nodes are bound to the stream of THIS step; a later capture that
+        # reused them would depend on uncaptured work)
+        return loss.detach(), getattr(self.criterion, "last_stats", None)
 
     def _slot(self, x, t):
         """Static buffers + graph per batch shape (a smaller last batch gets its own slot and
@@ -87,8 +90,22 @@ class TrainStep:
         nv.reset_launch_count()
         g = torch.cuda.CUDAGraph()
         step_before = getattr(opt, "_step", None)
-        with torch.cuda.graph(g):
-            loss, stats = self._eager(slot["sx"], slot["st"])
+        if hasattr(opt, "refresh_hyper"):
+            # values that change every step (Adam's bias corrections) go into the pinned block now: the
+            # refresh inside the captured iteration then finds nothing to change and nothing to wait for
+            opt.refresh_hyper(enqueue_copy=False)
+        try:
+            with torch.cuda.graph(g):
+                loss, stats = self._eager(slot["sx"], slot["st"])
+        except RuntimeError as e:
+            text = f"{e} {e.__context__ or ''}"
+            if "uncaptured work" in text or "StreamCaptureIsolation" in text:
+                raise RuntimeError(
+                    "TrainStep: the capture of the step's CUDA graph met work outside the capture -- most "
+                    "likely the autograd graph of an eager forward through this model is still alive (a loss "
+                    "or output tensor of it is referenced).  Delete it before the step captures (after "
+                    f"{self.warmup} warm-up calls), or construct the step with graph=False.") from e
+            raise
         if step_before is not None:
             opt._step = step_before  # capture does not execute; replays advance the counter
         self.launches_per_step = nv.launch_count()

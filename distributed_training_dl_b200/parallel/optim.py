@@ -124,21 +124,28 @@ class _FusedBase(torch.optim.Optimizer):
         every replay, so calling this with ``enqueue_copy=False`` before a replay is enough."""
         vals = self._hyper_values(self._world())
         new = torch.tensor(vals, dtype=torch.float32)
+        # Under stream capture nothing executes and the CUDA runtime refuses event waits from the host
+        # (they would invalidate the capture): the capturing caller (engine.TrainStep._capture,
+        # DataParallelStep) refreshes the block and drains earlier work BEFORE it starts the capture.
+        capturing = self._hyper_host.is_pinned() and torch.cuda.is_current_stream_capturing()
         if not torch.equal(self._hyper_host[: len(vals)], new):
             # The block is about to change while an earlier step's copy of it (enqueued below, or a
             # node of a replayed graph) may not have run yet: that step must not see the new values.
-            for ev in self._hyper_guards:
-                ev.synchronize()
+            if not capturing:
+                for ev in self._hyper_guards:
+                    ev.synchronize()
             self._hyper_host[: len(vals)] = new
-        self._hyper_guards = []
+        if not capturing:
+            self._hyper_guards = []
         if enqueue_copy:
             for h in self._hyper_devs:
                 if h is not None:
                     with torch.cuda.device(h.device):
                         h.copy_(self._hyper_host, non_blocking=True)
-                        ev = torch.cuda.Event()
-                        ev.record()
-                        self._hyper_guards.append(ev)
+                        if not capturing:       # an event recorded into a capture cannot be waited for
+                            ev = torch.cuda.Event()
+                            ev.record()
+                            self._hyper_guards.append(ev)
 
     def guard_hyper(self, event):
         """``event`` completes after a consumer of the pinned block (a graph replay) has read it."""

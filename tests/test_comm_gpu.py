@@ -1,4 +1,5 @@
-"""Peer-memory collectives and DDP-style training on >= 2 GPUs (skipped on a 1-GPU box)."""
+"""Peer-memory collectives and DDP-style training on >= 2 GPUs (skipped on a 1-GPU box), plus the
+single-replica variants of the single-process engine and front-end checks that a 1-GPU box can run."""
 import os
 
 import pytest
@@ -101,6 +102,21 @@ def test_data_parallel_engine_one_gpu(tmp_path):
     res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
                          env=dict(os.environ, CUDA_VISIBLE_DEVICES="0", DTDL_NVLS="0"))
     assert res.returncode == 0 and os.path.exists(tmp_path / "ok_dp"), res.stdout[-2000:] + res.stderr[-4000:]
+
+
+def test_frontends_one_gpu(tmp_path):
+    """The Keras- and Chainer-shaped front ends on ONE visible GPU (what a 1-GPU box can run of
+    ``test_frontends_on_all_gpus``): MirroredStrategy.fit with the fused Keras-Adam, ModelCheckpoint,
+    load_weights into a model whose step graph is already captured, ParallelUpdater in a Trainer."""
+    if torch.cuda.device_count() < 1:
+        pytest.skip("needs a GPU")
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    code = f"import sys; sys.path.insert(0, {here!r}); import _gpu_workers as w; w.frontends_multi_gpu({str(tmp_path)!r})"
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
+                         env=dict(os.environ, CUDA_VISIBLE_DEVICES="0", DTDL_NVLS="0"))
+    assert res.returncode == 0 and os.path.exists(tmp_path / "ok_fe"), res.stdout[-2000:] + res.stderr[-4000:]
 
 
 @pytest.mark.parametrize("backend", ["b200", "nccl"])
