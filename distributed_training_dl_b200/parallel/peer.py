@@ -163,6 +163,7 @@ class PeerComm:
         self._fdchan = None
         self._deferred = False
         self._trace = None
+        self._last_stream = None    # stream of the last collective (see _stream)
 
     # ------------------------------------------------------------------ construction
     @classmethod
@@ -396,8 +397,19 @@ class PeerComm:
         return nv.lib().dtdl_multicast_supported(self.device.index or 0) == 1
 
     # ------------------------------------------------------------------ collectives
-    def _stream(self, stream):
-        return (stream or torch.cuda.current_stream(self.device)).cuda_stream
+    def _stream(self, stream, collective=True):
+        """The stream a call runs on.  All collectives of one communicator share one pair of flag rows
+        and device-resident epochs, so they must execute in issue order: when a collective is issued
+        on another stream than the previous one, the new stream first waits for the old one.  (Not
+        under stream capture, where a wait on outside work is illegal; the reducer keeps every
+        collective of a captured step on its one communication stream.)"""
+        s = stream or torch.cuda.current_stream(self.device)
+        if collective:
+            last = self._last_stream
+            if last is not None and last != s and not torch.cuda.is_current_stream_capturing():
+                s.wait_stream(last)
+            self._last_stream = s
+        return s.cuda_stream
 
     # Variant per message size, per world size, from the measured sweeps (profiles/round2/w{4,8}/
     # allreduce_sweep_*.md, profiles/allreduce_sweep_2gpu.md): rows of (largest message in bytes, variant),
@@ -476,7 +488,7 @@ class PeerComm:
 
     def trace_mark(self, stream=None):
         """A time stamp on ``stream`` (e.g. right after the last backward kernel)."""
-        nv.call("comm_trace_mark", self.handle, 7, self._stream(stream))
+        nv.call("comm_trace_mark", self.handle, 7, self._stream(stream, collective=False))
 
     def trace_end(self):
         nv.lib().dtdl_comm_trace(self.handle, None, 0)

@@ -13,8 +13,9 @@ from _common import cifar_dataset, dtdl, pytorch_flags, train_epoch  # noqa: E40
 
 def main():
     args = pytorch_flags("B200-native CIFAR-10 training, single-process data parallel").parse_args()
-    if args.gpu_nums < 2 or torch.cuda.device_count() < args.gpu_nums:
-        raise SystemExit(f"data_parallel.py needs -g >= 2 visible GPUs (have {torch.cuda.device_count()})")
+    if args.gpu_nums < 1 or torch.cuda.device_count() < args.gpu_nums:
+        raise SystemExit(f"data_parallel.py needs -g N with 1 <= N <= visible GPUs (have {torch.cuda.device_count()}); "
+                         "one GPU runs a single replica, as nn.DataParallel does")
     torch.manual_seed(args.seed)
     device = torch.device("cuda:0")
     loader = torch.utils.data.DataLoader(cifar_dataset(args), batch_size=args.batch_size, shuffle=True,

@@ -423,3 +423,14 @@ def test_collective_variant_table(tmp_path, monkeypatch):
     pc.world, pc.use_nvls = 8, True
     assert pc.choose_two_shot(4096) == 0 and pc.choose_two_shot(1 << 20) == 2
     PeerComm._variant_table = None
+
+
+def test_train_step_returns_a_detached_loss():
+    """The step has already run backward; a caller that keeps the loss must not keep the graph."""
+    from distributed_training_dl_b200.engine import CrossEntropyLoss, TrainStep
+    torch.manual_seed(0)
+    net = MLP(32)
+    opt = dtdl.FusedSGD(net.parameters(), lr=0.1)
+    step = TrainStep(net, opt, CrossEntropyLoss())
+    loss = step(torch.randn(8, 784), torch.randint(0, 10, (8,)))
+    assert loss.grad_fn is None and not loss.requires_grad and loss.item() > 0

@@ -145,3 +145,28 @@ def test_weights_loaded_into_a_captured_step_are_used_by_the_next_replay():
     net.load_state_dict(sd)
     after = step(x, t).item()          # a replay; lr = 0, so nothing else changes
     assert abs(after - math.log(10)) < 1e-4, (before, after)
+
+
+def test_keeping_the_returned_loss_does_not_break_the_capture():
+    """``Model.fit`` keeps each step's loss until the next call returns.  The loss of an eager warm-up
+    step used to carry that step's autograd graph, whose gradient-accumulation nodes are bound to the
+    eager stream; the capture of the next call then failed with "dependency created on uncaptured
+    work".  The step now returns a detached loss, with an optimizer whose hyper-parameters change
+    every step (Adam) as well."""
+    import distributed_training_dl_b200 as dtdl
+    from distributed_training_dl_b200.engine import CrossEntropyLoss, TrainStep
+    from distributed_training_dl_b200.models import MnistCNN
+    torch.manual_seed(0)
+    net = dtdl.wrap(MnistCNN().cuda())
+    opt = dtdl.FusedAdam(net.parameters(), lr=1e-3, keras=True)
+    step = TrainStep(net, opt, CrossEntropyLoss(), graph=True, warmup=2)
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(32, 1, 28, 28, generator=g).pin_memory()
+    t = torch.randint(0, 10, (32,), generator=g).pin_memory()
+    kept, losses = None, []
+    for _ in range(6):
+        kept = step(x, t)               # the previous ``kept`` is alive during this call
+        assert kept.grad_fn is None
+        losses.append(kept.item())
+    assert step.launches_per_step and step.launches_per_step > 0      # the graph was captured
+    assert losses[-1] < losses[0], losses                             # same batch: the loss goes down
