@@ -401,6 +401,11 @@ class DistributedModel(nn.Module):
         """For stock torch optimizers: call before ``optimizer.step()`` (a fused optimizer does it)."""
         self.reducer.wait()
 
+    def sync_parameters(self):
+        """Rank 0's parameters and buffers become everyone's again (the broadcast ``wrap`` does at
+        construction): call it on every rank after loading weights on rank 0 only."""
+        self.reducer.sync_parameters()
+
 
 def wrap(model, optimizer=None, comm=None, **kw) -> DistributedModel:
     """``net = wrap(net)`` replaces ``DistributedDataParallel(net, device_ids=[gpu])``.

@@ -84,6 +84,15 @@ def ddp_equivalence(i, world, init_kind, port, outdir):
     dtdl.save_model(net.module, os.path.join(outdir, "ddp.pth"), per_rank=True)
     comm.barrier()
     assert os.path.exists(os.path.join(outdir, f"ddp_{i}.pth"))
+    # (e) weights loaded on rank 0 alone reach everyone through net.sync_parameters()
+    if i == 0:
+        with torch.no_grad():
+            for p in net.module.parameters():
+                p.add_(1.0)
+    net.sync_parameters()
+    for p in net.parameters():
+        allp = _gather(comm, p)
+        assert all(torch.equal(allp[0], q) for q in allp)
     open(os.path.join(outdir, f"ok_{i}"), "w").write("ok")
     dtdl.shutdown()
 
