@@ -6,7 +6,6 @@ import torch
 from distributed_training_dl_b200 import strategy as ks
 from distributed_training_dl_b200 import trainer as ch
 from distributed_training_dl_b200.models import MLP, MnistCNN
-from distributed_training_dl_b200.utils import SyntheticDataset
 
 
 def _separable(n, shape, seed=0):

@@ -4,7 +4,7 @@ import sys
 import torch
 sys.path.insert(0, ".")
 from distributed_training_dl_b200 import _native as nv
-from distributed_training_dl_b200.ops import BatchNorm2d, Conv2d, functional as fn
+from distributed_training_dl_b200.ops import Conv2d, functional as fn
 from distributed_training_dl_b200.utils.timing import flush_l2
 
 

@@ -1,7 +1,6 @@
 """Tiny run of every single-GPU kernel for `compute-sanitizer --tool memcheck` (one tool per call)."""
 import sys
 import torch
-import torch.nn.functional as F
 sys.path.insert(0, ".")
 import distributed_training_dl_b200 as dtdl
 from distributed_training_dl_b200.models import PyramidNet, MnistCNN, MLP
