@@ -5,7 +5,6 @@ import os
 import sys
 import time
 
-
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import distributed_training_dl_b200 as dtdl  # noqa: E402
 
